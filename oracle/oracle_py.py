@@ -1,0 +1,121 @@
+"""oracle/oracle_py.py — TEST INFRASTRUCTURE ONLY: ctypes bindings of the checkers.
+
+  RefOracle  : oracle/_ref/libref_{strict,fast}.so — the reference's own kernel text compiled as C++
+  PortOracle : oracle/lib/liboracle_port.so        — the plain-C restatement (oracle/rt_oracle.c)
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+TABLE_FLOATS = 400000
+
+
+class SceneDesc(C.Structure):
+    """Layout shared by ref_scene_desc (oracle) and rt_scene_desc (include/rt_capi.h)."""
+    _fields_ = [(n, C.c_void_p) for n in
+                ("materials", "spheres", "planes", "lenses", "vertices", "uvs", "indices", "meshes", "models")] + \
+               [(n, C.c_uint32) for n in
+                ("n_materials", "n_spheres", "n_planes", "n_lenses", "n_vertices", "n_uvs", "n_indices", "n_meshes",
+                 "n_models")]
+
+
+def make_desc(arr):
+    """arr: dict of numpy arrays in the reference AoS layouts (see scene_py.Scene.arrays)."""
+    keep = {}
+    d = SceneDesc()
+    for name in ("materials", "spheres", "planes", "lenses", "vertices", "uvs", "indices", "meshes", "models"):
+        a = np.ascontiguousarray(arr[name])
+        keep[name] = a
+        setattr(d, name, a.ctypes.data if a.size else None)
+        setattr(d, "n_" + name, a.shape[0])
+    d._keep = keep
+    return d
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class RefOracle:
+    def __init__(self, flavour="strict"):
+        path = os.path.join(HERE, "_ref", "libref_%s.so" % flavour)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " (build with `make -C oracle ref` where /root/reference exists)")
+        L = self.lib = C.CDLL(path)
+        L.ref_render.restype = C.c_double
+        L.ref_render.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
+                                 C.POINTER(C.c_uint64)]
+        L.ref_make_table.argtypes = [C.c_uint32, C.c_void_p]
+        L.ref_hit.restype = C.c_int
+        L.ref_hit.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_primary_ids.restype = C.c_int
+        L.ref_primary_ids.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.ref_identify.restype = C.c_uint32
+        L.ref_identify.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_bounce.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                 C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.ref_build_info.restype = C.c_char_p
+
+    def build_info(self):
+        return self.lib.ref_build_info().decode()
+
+    def make_table(self, seed):
+        t = np.empty(TABLE_FLOATS, dtype=np.float32)
+        self.lib.ref_make_table(seed, t.ctypes.data)
+        return t
+
+    def render(self, desc, tex, cam, table, W, H, first, n, depth=30, threads=None, image=None):
+        """Returns (image RGBA f32 [H,W,4] = sqrt(running mean), rays, seconds)."""
+        tex = _tex(tex)
+        if image is None:
+            image = np.zeros((H, W, 4), dtype=np.float32)
+        rays = C.c_uint64(0)
+        cam = np.ascontiguousarray(cam, dtype=np.float32)
+        secs = self.lib.ref_render(C.byref(desc), tex.ctypes.data, tex.shape[2], tex.shape[1], tex.shape[0],
+                                   cam.ctypes.data, table.ctypes.data, image.ctypes.data, W, H, first, n, depth,
+                                   threads or os.cpu_count(), C.byref(rays))
+        return image, rays.value, secs
+
+    def hit(self, desc, origin, direction):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        out = np.zeros(9, dtype=np.float32)
+        ids = np.zeros(2, dtype=np.uint32)
+        h = self.lib.ref_hit(C.byref(desc), o.ctypes.data, d.ctypes.data, out.ctypes.data, ids.ctypes.data)
+        return bool(h), out, ids
+
+    def identify(self, desc, origin, direction):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        t = C.c_float(0)
+        i = self.lib.ref_identify(C.byref(desc), o.ctypes.data, d.ctypes.data, C.byref(t))
+        return i, t.value
+
+    def primary_ids(self, desc, cam, W, H):
+        ids = np.zeros((H, W), dtype=np.uint32)
+        ts = np.zeros((H, W), dtype=np.float32)
+        cam = np.ascontiguousarray(cam, dtype=np.float32)
+        bad = self.lib.ref_primary_ids(C.byref(desc), cam.ctypes.data, W, H, ids.ctypes.data, ts.ctypes.data)
+        return ids, ts, bad
+
+    def bounce(self, desc, tex, table, ray6, s_seed, gx, gy):
+        tex = _tex(tex)
+        ray = np.array(ray6, dtype=np.float32)
+        col = np.zeros(3, dtype=np.float32)
+        self.lib.ref_bounce(C.byref(desc), tex.ctypes.data, tex.shape[2], tex.shape[1], tex.shape[0],
+                            table.ctypes.data, ray.ctypes.data, s_seed, gx, gy, col.ctypes.data)
+        return ray, col
+
+
+def _tex(tex):
+    if tex is None:
+        return np.zeros((1, 1, 1, 4), dtype=np.float32)
+    assert tex.dtype == np.float32 and tex.ndim == 4 and tex.shape[3] == 4
+    return np.ascontiguousarray(tex)
