@@ -1,0 +1,135 @@
+/* include/rt_capi.h — C ABI of the B200 path tracer (librtb200.so).
+ *
+ * This is the drop-in boundary for the reference's per-pixel path-tracing path.  Every entry point names
+ * the reference interface it replaces (paths relative to the reference repository).  The C++ classes in
+ * include/raytracer.h, include/scene.h and include/camera.h keep the reference's signatures and sit on top
+ * of exactly these functions.
+ *
+ * Conventions: every function returns 0 on success and a non-zero rt_status on failure; the message of the
+ * last failure on the calling thread is returned by rt_last_error().  Nothing throws, nothing calls exit().
+ * A context belongs to one CUDA device and is used from one host thread at a time.  Calls are synchronous
+ * (the reference finishes its queue after every launch, src/raytracer.cpp:140,161) unless named *_async.
+ * There is no CPU fallback: without a usable CUDA device rt_create fails with RT_ERR_CUDA.
+ */
+#ifndef RT_CAPI_H
+#define RT_CAPI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = 1,   /* bad argument / scene validation failed */
+    RT_ERR_CUDA = 2,      /* CUDA runtime error (message has the CUDA string) */
+    RT_ERR_STATE = 3,     /* call order (e.g. render before a scene was uploaded) */
+    RT_ERR_UNSUPPORTED = 4
+} rt_status;
+
+/* Pointers + counts to the reference's HOST array-of-structs layouts (include/scene.h:32-81; a cl_float3 is
+ * 16 bytes): Material 48 B, Sphere 32 B, Plane 48 B, Lens 64 B, vertex 16 B, uv 8 B, index 4 B, Mesh 16 B,
+ * Model 12 B.  Replaces the nine cl::Buffer writes + the createScene kernel of
+ * src/scene.cpp:71-108 / kernels/raytracer.cl:541-558. */
+typedef struct rt_scene_desc {
+    const void *materials, *spheres, *planes, *lenses, *vertices, *uvs, *indices, *meshes, *models;
+    uint32_t n_materials, n_spheres, n_planes, n_lenses, n_vertices, n_uvs, n_indices, n_meshes, n_models;
+} rt_scene_desc;
+
+enum { RT_RNG_TABLE = 0,      /* the reference's hashed 400 000-float table, kernels/raytracer.cl:113-125 */
+       RT_RNG_COUNTER = 1 };  /* counter-based per-pixel generator — same sampling law */
+enum { RT_ARITH_STRICT = 0,   /* unfused IEEE binary32 in the oracle's operation order (bit-exact arm) */
+       RT_ARITH_FAST = 1 };   /* FMA contraction, approximate rcp/rsqrt/sqrt (throughput arm) */
+enum { RT_ACCUM_REFERENCE = 0,/* image = (sqrt(running mean),1), kernels/raytracer.cl:509,524-531 */
+       RT_ACCUM_SUM = 1 };    /* accum.rgb += radiance, accum.a += 1 (what the sample split reduces) */
+enum { RT_MESH_FIRST_FRONT = 0, /* first front-facing face in order per mesh, kernels/raytracer.cl:291-303 */
+       RT_MESH_NEAREST = 1 };   /* nearest front-facing face, ties -> lowest face (BVH-compatible rule) */
+enum { RT_ACCEL_AUTO = 0, RT_ACCEL_BRUTE = 1, RT_ACCEL_BVH = 2 };
+
+typedef struct rt_params {
+    uint32_t max_depth;   /* reference: #define DEPTH 30 (kernels/raytracer.cl:5) */
+    uint32_t rng_mode;    /* RT_RNG_*   */
+    uint32_t seed;        /* key of the counter generator */
+    uint32_t arith;       /* RT_ARITH_* */
+    uint32_t mesh_mode;   /* RT_MESH_*  */
+    uint32_t accel;       /* RT_ACCEL_* */
+} rt_params;
+
+typedef struct rt_stats {
+    uint64_t rays_total;      /* nearest-hit queries (path segments) since the last rt_render / rt_clear_accum */
+    uint64_t rays_last;       /* ... of the last render call */
+    double   ms_last;         /* device time of the last render call (CUDA events on the context's stream) */
+    uint32_t samples_done;    /* samples accumulated in the image / accumulation buffer */
+    uint32_t kernel_launches; /* kernels launched by this context since creation */
+    uint32_t n_primitives;    /* spheres + planes + lenses + triangles on the device */
+    uint32_t bvh_nodes;       /* 0 when the brute-force path is active */
+} rt_stats;
+
+#define RT_ID_MISS 0xFFFFFFFFu   /* primary id = kind << 28 | index; kind 1 sphere, 2 plane, 3 lens, 4 triangle */
+#define RT_RANDOM_TABLE_FLOATS 400000u
+
+const char* rt_last_error(void);
+const char* rt_version(void);
+
+/* KernelGL::KernelGL + RayTracer::RayTracer (src/kernelgl.cpp:20-27,58-93, src/raytracer.cpp:24-36): device
+ * pick, stream, image and accumulation buffers (the headless replacement of the CL/GL shared texture). */
+int rt_create(int width, int height, int device, rt_ctx** out);
+int rt_destroy(rt_ctx* ctx);
+/* Run the context's work on a caller-owned CUDA stream (cudaStream_t); NULL restores the private stream. */
+int rt_set_stream(rt_ctx* ctx, void* cuda_stream);
+
+/* SceneCreator::setupBuffers/createScene (src/scene.cpp:46-87).  Validates ids, converts to device SoA. */
+int rt_upload_scene(rt_ctx* ctx, const rt_scene_desc* scene);
+/* SceneCreator::loadTextures upload half (src/scene.cpp:164,173): equal-sized RGBA-f32 layers. */
+int rt_upload_textures(rt_ctx* ctx, const float* rgba, int width, int height, int layers);
+/* The random buffer of src/raytracer.cpp:67-93; rt_make_random_table reproduces that loop for a fixed seed. */
+int rt_make_random_table(uint32_t seed, float* out_400000);
+int rt_set_random_table(rt_ctx* ctx, const float* table, uint32_t n_floats);
+int rt_set_params(rt_ctx* ctx, const rt_params* params);
+int rt_get_params(rt_ctx* ctx, rt_params* params);
+
+/* RayTracer::render (src/raytracer.cpp:127-144): sample_counter = 0, one sample, overwrites the image. */
+int rt_render(rt_ctx* ctx, const float camera[12]);
+/* RayTracer::renderAgain (src/raytracer.cpp:146-165): ++sample_counter, one more sample, running mean. */
+int rt_render_again(rt_ctx* ctx, const float camera[12]);
+/* n_samples consecutive samples [first, first+n) in ONE launch.  accum_mode RT_ACCUM_REFERENCE continues the
+ * reference's sqrt(mean) chain in the image (first == 0 restarts it; bit-identical to render + renderAgain
+ * x (n-1)); RT_ACCUM_SUM adds into the linear accumulation buffer (sample indices are global, so disjoint
+ * ranges rendered on different GPUs can be summed). */
+int rt_render_samples(rt_ctx* ctx, const float camera[12], uint32_t first, uint32_t n_samples, uint32_t accum_mode);
+int rt_clear_accum(rt_ctx* ctx);
+/* image = (sqrt(accum.rgb / spp), 1): the tail of kernels/raytracer.cl:509,531 applied to a summed buffer. */
+int rt_finalize(rt_ctx* ctx, uint32_t total_spp);
+
+/* Read-backs (the reference never reads back; its image lives in a GL texture, src/raytracer.cpp:167-174).
+ * Row 0 is t = 0 (kernels/raytracer.cl:500-501), i.e. the bottom row on screen (shaders/screen.vs:7). */
+int rt_read_image(rt_ctx* ctx, float* rgba);                  /* width*height*4 floats */
+int rt_read_accum(rt_ctx* ctx, float* rgba);                  /* width*height*4 floats */
+int rt_read_primary_ids(rt_ctx* ctx, const float camera[12], uint32_t* ids, float* t);
+int rt_get_stats(rt_ctx* ctx, rt_stats* stats);
+
+/* Device-side access for the multi-GPU sample split (one process per GPU; the caller reduces the buffer with
+ * NCCL): pointer to the W*H float4 accumulation buffer, or make the context accumulate into a caller buffer. */
+int rt_accum_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
+int rt_image_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
+int rt_set_accum_device_buffer(rt_ctx* ctx, void* device_ptr, size_t bytes);
+
+/* Probes used by the parity tests: nearest hit of arbitrary rays, and one bounce of the path loop.
+ * rays6 = n x (origin.xyz, dir.xyz) on the host.  out_t/out_id may be NULL. */
+int rt_trace_rays(rt_ctx* ctx, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t);
+/* In-place bounce as work-item (gx, gy): rays6 updated, col3 = throughput after the bounce from (1,1,1),
+ * ended[i] = 1 when the path terminated (miss or light). */
+int rt_bounce_rays(rt_ctx* ctx, float* rays6, uint32_t n, const uint32_t* sample, const uint32_t* bounce,
+                   const uint32_t* gx, const uint32_t* gy, float* col3, uint8_t* ended);
+
+/* Measured FP32 issue peak of the device (dependent-free FFMA loop on every SM): G lane-instructions/s. */
+int rt_measure_fp32_peak(int device, double* gslots_per_s, double* sm_clock_mhz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_CAPI_H */

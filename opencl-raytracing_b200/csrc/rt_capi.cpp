@@ -1,0 +1,614 @@
+// csrc/rt_capi.cpp — host side of the C ABI (include/rt_capi.h): context, device buffers, scene conversion
+// from the reference's host AoS layouts to the device test stream, launches, read-backs.
+//
+// This layer takes over the roles of KernelGL (src/kernelgl.cpp: device/context/queue), of
+// RayTracer::createCLBuffers/setKernelArgs/render/renderAgain (src/raytracer.cpp:63-165) and of
+// SceneCreator::setupBuffers/createScene (src/scene.cpp:46-87) in the reference.
+#include "../../include/rt_capi.h"
+#include "rt_device.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <string>
+#include <vector>
+
+using namespace rtb;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) return fail(RT_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_));     \
+    } while (0)
+
+// Host AoS records, include/scene.h:32-81 (cl_float3 = 16 bytes)
+struct HMaterial { int32_t type; int32_t pad0[3]; float color[4]; float extra; float pad1[3]; };
+struct HSphere { float pos[4]; float r; uint32_t mat; float pad[2]; };
+struct HPlane { float pos[4]; float normal[4]; uint32_t mat; float pad[3]; };
+struct HLens { float pos[4]; float p1[4]; float p2[4]; float r1, r2; uint32_t mat; float pad; };
+struct HMesh { uint32_t vertex_anchor, index_anchor, face_count, texture_id; };
+struct HModel { uint32_t mesh_anchor, mesh_count, mat; };
+static_assert(sizeof(HMaterial) == 48 && sizeof(HSphere) == 32 && sizeof(HPlane) == 48 && sizeof(HLens) == 64 &&
+              sizeof(HMesh) == 16 && sizeof(HModel) == 12, "reference host layouts");
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t s) {
+        release();
+        n = v.size();
+        cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
+        if (e != cudaSuccess) return e;
+        if (n) e = cudaMemcpyAsync(p, v.data(), n * sizeof(T), cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return e;
+        return cudaStreamSynchronize(s);
+    }
+};
+
+}  // namespace
+
+struct rt_ctx {
+    int device = 0, W = 0, H = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float4* d_image = nullptr;
+    float4* d_accum_own = nullptr;
+    float4* d_accum = nullptr;      // own or caller-supplied
+    unsigned long long* d_rays = nullptr;
+    float* d_table = nullptr;
+    float4* d_tex = nullptr;
+    DevTexture tex{nullptr, 1, 1, 1};
+    bool have_scene = false;
+    DevScene sc{};
+    DevBuf<float4> b_stream, b_sph_shade, b_pla_normal, b_len_shade, b_mat;
+    DevBuf<uint32_t> b_sph_mat, b_pla_mat, b_len_mat, b_tri_mesh;
+    DevBuf<float2> b_tri_uv;
+    DevBuf<MeshInst> b_mesh;
+    rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
+    uint32_t sample_counter = 0;
+    rt_stats stats{};
+};
+
+namespace {
+
+struct Guard {   // make the context's device current for the duration of a call
+    int prev = -1;
+    bool ok = true;
+    explicit Guard(const rt_ctx* c) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != c->device && cudaSetDevice(c->device) != cudaSuccess) ok = false;
+    }
+    ~Guard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+inline void sub3(const float* a, const float* b, float* r) { r[0] = a[0] - b[0]; r[1] = a[1] - b[1]; r[2] = a[2] - b[2]; }
+
+// Reference AoS -> device test stream + shade arrays.  All float precomputation is a single correctly
+// rounded operation per value (this file is built with -ffp-contract=off), so e1, e2, r*r and the unit
+// normal are bit-identical to what kernels/raytracer.cl computes per ray.
+int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
+    const HMaterial* mats = (const HMaterial*)d->materials;
+    const HSphere* sph = (const HSphere*)d->spheres;
+    const HPlane* pla = (const HPlane*)d->planes;
+    const HLens* len = (const HLens*)d->lenses;
+    const float* vtx = (const float*)d->vertices;
+    const float* uvs = (const float*)d->uvs;
+    const uint32_t* idx = (const uint32_t*)d->indices;
+    const HMesh* meshes = (const HMesh*)d->meshes;
+    const HModel* models = (const HModel*)d->models;
+
+    if (d->n_materials == 0) return fail(RT_ERR_INVALID, "scene has no materials");
+    if ((d->n_materials && !mats) || (d->n_spheres && !sph) || (d->n_planes && !pla) || (d->n_lenses && !len) ||
+        (d->n_vertices && !vtx) || (d->n_indices && !idx) || (d->n_meshes && !meshes) || (d->n_models && !models))
+        return fail(RT_ERR_INVALID, "null array with non-zero count");
+    for (uint32_t i = 0; i < d->n_materials; ++i)
+        if (mats[i].type < 0 || mats[i].type > 5) return fail(RT_ERR_INVALID, "material %u has unknown type %d", i, mats[i].type);
+    auto is_textured = [&](uint32_t m) { return mats[m].type == 4; };
+
+    std::vector<float4> stream, sph_shade, pla_normal, len_shade, mat;
+    std::vector<uint32_t> sph_mat, pla_mat, len_mat, tri_mesh;
+    std::vector<float2> tri_uv;
+    std::vector<MeshInst> inst;
+
+    for (uint32_t i = 0; i < d->n_spheres; ++i) {
+        if (sph[i].mat >= d->n_materials) return fail(RT_ERR_INVALID, "sphere %u: material %u does not exist", i, sph[i].mat);
+        if (is_textured(sph[i].mat)) return fail(RT_ERR_UNSUPPORTED, "sphere %u: textured material on a non-mesh primitive (uninitialised uv in the reference)", i);
+        stream.push_back(make_float4(sph[i].pos[0], sph[i].pos[1], sph[i].pos[2], sph[i].r * sph[i].r));
+        sph_shade.push_back(make_float4(sph[i].pos[0], sph[i].pos[1], sph[i].pos[2], sph[i].r));
+        sph_mat.push_back(sph[i].mat);
+    }
+    const uint32_t off_pla = (uint32_t)stream.size();
+    for (uint32_t i = 0; i < d->n_planes; ++i) {
+        if (pla[i].mat >= d->n_materials) return fail(RT_ERR_INVALID, "plane %u: material %u does not exist", i, pla[i].mat);
+        if (is_textured(pla[i].mat)) return fail(RT_ERR_UNSUPPORTED, "plane %u: textured material on a non-mesh primitive", i);
+        stream.push_back(make_float4(pla[i].pos[0], pla[i].pos[1], pla[i].pos[2], 0.0f));
+        stream.push_back(make_float4(pla[i].normal[0], pla[i].normal[1], pla[i].normal[2], 0.0f));
+        pla_normal.push_back(make_float4(pla[i].normal[0], pla[i].normal[1], pla[i].normal[2], 0.0f));
+        pla_mat.push_back(pla[i].mat);
+    }
+    const uint32_t off_len = (uint32_t)stream.size();
+    for (uint32_t i = 0; i < d->n_lenses; ++i) {
+        if (len[i].mat >= d->n_materials) return fail(RT_ERR_INVALID, "lens %u: material %u does not exist", i, len[i].mat);
+        if (is_textured(len[i].mat)) return fail(RT_ERR_UNSUPPORTED, "lens %u: textured material on a non-mesh primitive", i);
+        stream.push_back(make_float4(len[i].p1[0], len[i].p1[1], len[i].p1[2], len[i].r1 * len[i].r1));
+        stream.push_back(make_float4(len[i].p2[0], len[i].p2[1], len[i].p2[2], len[i].r2 * len[i].r2));
+        len_shade.push_back(make_float4(len[i].p1[0], len[i].p1[1], len[i].p1[2], len[i].r1));
+        len_shade.push_back(make_float4(len[i].p2[0], len[i].p2[1], len[i].p2[2], len[i].r2));
+        len_mat.push_back(len[i].mat);
+    }
+    const uint32_t off_tri = (uint32_t)stream.size();
+    uint32_t n_tri = 0;
+    for (uint32_t mo = 0; mo < d->n_models; ++mo) {
+        const HModel& M = models[mo];
+        if (M.mat >= d->n_materials) return fail(RT_ERR_INVALID, "ERROR: MATERIAL OF ID: %u DOES NOT EXIST", M.mat);
+        if ((uint64_t)M.mesh_anchor + M.mesh_count > d->n_meshes) return fail(RT_ERR_INVALID, "model %u: mesh range out of bounds", mo);
+        for (uint32_t k = 0; k < M.mesh_count; ++k) {
+            const HMesh& me = meshes[M.mesh_anchor + k];
+            if ((uint64_t)me.index_anchor + 3ull * me.face_count > d->n_indices) return fail(RT_ERR_INVALID, "mesh %u: index range out of bounds", M.mesh_anchor + k);
+            if (is_textured(M.mat) && me.texture_id >= (uint32_t)c->tex.layers && c->d_tex)
+                return fail(RT_ERR_INVALID, "mesh %u: texture %u does not exist", M.mesh_anchor + k, me.texture_id);
+            MeshInst mi{};
+            mi.tri_first = n_tri; mi.tri_count = me.face_count; mi.face_id_base = me.index_anchor / 3u;
+            mi.mat_id = M.mat; mi.texture_id = me.texture_id;
+            double cx = 0, cy = 0, cz = 0;
+            std::vector<const float*> corners;
+            for (uint32_t f = 0; f < me.face_count; ++f) {
+                const float* P[3];
+                float2 uv[3];
+                for (int j = 0; j < 3; ++j) {
+                    const uint64_t vi = (uint64_t)me.vertex_anchor + idx[me.index_anchor + 3 * f + j];  // kernels/raytracer.cl:93-99
+                    if (vi >= d->n_vertices) return fail(RT_ERR_INVALID, "mesh %u: vertex index out of bounds", M.mesh_anchor + k);
+                    P[j] = vtx + 4 * vi;
+                    uv[j] = (uvs && vi < d->n_uvs) ? make_float2(uvs[2 * vi], uvs[2 * vi + 1]) : make_float2(0.0f, 0.0f);
+                    corners.push_back(P[j]);
+                    cx += P[j][0]; cy += P[j][1]; cz += P[j][2];
+                }
+                float e1[3], e2[3];
+                sub3(P[1], P[0], e1);
+                sub3(P[2], P[0], e2);
+                const float nx = e1[1] * e2[2] - e1[2] * e2[1], ny = e1[2] * e2[0] - e1[0] * e2[2], nz = e1[0] * e2[1] - e1[1] * e2[0];
+                const float inv = 1.0f / std::sqrt(nx * nx + ny * ny + nz * nz);
+                stream.push_back(make_float4(P[0][0], P[0][1], P[0][2], e1[0]));
+                stream.push_back(make_float4(e1[1], e1[2], e2[0], e2[1]));
+                stream.push_back(make_float4(e2[2], nx * inv, ny * inv, nz * inv));
+                tri_uv.push_back(uv[0]); tri_uv.push_back(uv[1]); tri_uv.push_back(uv[2]);
+                tri_mesh.push_back((uint32_t)inst.size());
+                ++n_tri;
+            }
+            if (!corners.empty()) {
+                cx /= corners.size(); cy /= corners.size(); cz /= corners.size();
+                double r2 = 0;
+                for (const float* q : corners) {
+                    const double dx = q[0] - cx, dy = q[1] - cy, dz = q[2] - cz;
+                    r2 = std::fmax(r2, dx * dx + dy * dy + dz * dz);
+                }
+                mi.bound[0] = (float)cx; mi.bound[1] = (float)cy; mi.bound[2] = (float)cz;
+                mi.bound[3] = (float)(std::sqrt(r2) * 1.001 + 1e-4);
+            }
+            inst.push_back(mi);
+        }
+    }
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        float t;
+        std::memcpy(&t, &mats[i].type, 4);
+        mat.push_back(make_float4(t, mats[i].extra, 0.0f, 0.0f));
+        mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
+    }
+    const size_t staged = (stream.size() + 3 * inst.size()) * sizeof(float4);
+    if (staged > kMaxStagedBytes)
+        return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); BVH path required", staged, kMaxStagedBytes);
+
+    cudaStream_t s = c->stream;
+    CU(c->b_stream.upload(stream, s));       CU(c->b_sph_shade.upload(sph_shade, s)); CU(c->b_sph_mat.upload(sph_mat, s));
+    CU(c->b_pla_normal.upload(pla_normal, s)); CU(c->b_pla_mat.upload(pla_mat, s));
+    CU(c->b_len_shade.upload(len_shade, s)); CU(c->b_len_mat.upload(len_mat, s));
+    CU(c->b_tri_uv.upload(tri_uv, s));       CU(c->b_tri_mesh.upload(tri_mesh, s));
+    CU(c->b_mesh.upload(inst, s));           CU(c->b_mat.upload(mat, s));
+
+    DevScene& sc = c->sc;
+    sc.stream = c->b_stream.p; sc.stream_f4 = (uint32_t)stream.size();
+    sc.n_sph = d->n_spheres; sc.n_pla = d->n_planes; sc.n_len = d->n_lenses; sc.n_tri = n_tri; sc.n_mesh = (uint32_t)inst.size();
+    sc.off_pla = off_pla; sc.off_len = off_len; sc.off_tri = off_tri;
+    sc.mesh = c->b_mesh.p;
+    sc.sph_shade = c->b_sph_shade.p; sc.sph_mat = c->b_sph_mat.p;
+    sc.pla_normal = c->b_pla_normal.p; sc.pla_mat = c->b_pla_mat.p;
+    sc.len_shade = c->b_len_shade.p; sc.len_mat = c->b_len_mat.p;
+    sc.tri_uv = c->b_tri_uv.p; sc.tri_mesh = c->b_tri_mesh.p;
+    sc.mat = c->b_mat.p; sc.n_mat = d->n_materials;
+    c->stats.n_primitives = d->n_spheres + d->n_planes + d->n_lenses + n_tri;
+    c->stats.bvh_nodes = 0;
+    c->have_scene = true;
+    return RT_OK;
+}
+
+}  // namespace
+
+// ================================================================================================ API
+extern "C" {
+
+const char* rt_last_error(void) { return g_last_error.c_str(); }
+const char* rt_version(void) { return "rtb200 0.1 (sm_100a; strict+fast arithmetic; table+counter RNG)"; }
+
+int rt_create(int width, int height, int device, rt_ctx** out) {
+    if (!out) return fail(RT_ERR_INVALID, "rt_create: out is null");
+    *out = nullptr;
+    if (width <= 0 || height <= 0 || width > 65535 || height > 65535)
+        return fail(RT_ERR_INVALID, "rt_create: bad size %d x %d", width, height);
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(RT_ERR_CUDA, "rt_create: no CUDA device (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return fail(RT_ERR_INVALID, "rt_create: device %d out of range (0..%d)", device, n_dev - 1);
+    rt_ctx* c = new rt_ctx();
+    c->device = device; c->W = width; c->H = height;
+    Guard g(c);
+    const size_t px = (size_t)width * height;
+    auto bail = [&](cudaError_t err, const char* what) {
+        int r = fail(RT_ERR_CUDA, "rt_create: %s: %s", what, cudaGetErrorString(err));
+        rt_destroy(c);
+        return r;
+    };
+    if ((e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
+    c->stream = c->own_stream;
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "event");
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "event");
+    if ((e = cudaMalloc(&c->d_image, px * sizeof(float4))) != cudaSuccess) return bail(e, "image buffer");
+    if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4))) != cudaSuccess) return bail(e, "accumulation buffer");
+    if ((e = cudaMalloc(&c->d_rays, sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counter");
+    c->d_accum = c->d_accum_own;
+    cudaMemsetAsync(c->d_image, 0, px * sizeof(float4), c->stream);
+    cudaMemsetAsync(c->d_accum, 0, px * sizeof(float4), c->stream);
+    // 1x1x1 dummy texture array, as the reference creates for texture-less scenes (src/scene.cpp:188)
+    if ((e = cudaMalloc(&c->d_tex, sizeof(float4))) != cudaSuccess) return bail(e, "texture");
+    cudaMemsetAsync(c->d_tex, 0, sizeof(float4), c->stream);
+    c->tex = DevTexture{c->d_tex, 1, 1, 1};
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return bail(e, "init");
+    *out = c;
+    return RT_OK;
+}
+
+int rt_destroy(rt_ctx* c) {
+    if (!c) return RT_OK;
+    {
+        Guard g(c);
+        if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+        cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
+        c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
+        c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
+        c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_mesh.release();
+        if (c->ev0) cudaEventDestroy(c->ev0);
+        if (c->ev1) cudaEventDestroy(c->ev1);
+        if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    }
+    delete c;
+    return RT_OK;
+}
+
+int rt_set_stream(rt_ctx* c, void* s) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    return RT_OK;
+}
+
+int rt_upload_scene(rt_ctx* c, const rt_scene_desc* d) {
+    if (!c || !d) return fail(RT_ERR_INVALID, "rt_upload_scene: null argument");
+    Guard g(c);
+    c->have_scene = false;
+    return convert_scene(c, d);
+}
+
+int rt_upload_textures(rt_ctx* c, const float* rgba, int w, int h, int layers) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_upload_textures: null argument");
+    if (w <= 0 || h <= 0 || layers <= 0) return fail(RT_ERR_INVALID, "rt_upload_textures: bad size %d x %d x %d", w, h, layers);
+    Guard g(c);
+    const size_t n = (size_t)w * h * layers;
+    cudaFree(c->d_tex); c->d_tex = nullptr;
+    CU(cudaMalloc(&c->d_tex, n * sizeof(float4)));
+    CU(cudaMemcpyAsync(c->d_tex, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->tex = DevTexture{c->d_tex, w, h, layers};
+    return RT_OK;
+}
+
+// src/raytracer.cpp:67-93 with a caller-chosen seed instead of std::random_device.
+int rt_make_random_table(uint32_t seed, float* out) {
+    if (!out) return fail(RT_ERR_INVALID, "rt_make_random_table: null output");
+    const uint32_t N = RT_RANDOM_TABLE_FLOATS / 4;
+    std::mt19937 gen(seed);
+    std::uniform_real_distribution<float> uni(0.0f, 1.0f);
+    std::normal_distribution<float> nrm(0.0f, 1.0f);
+    for (uint32_t i = 0; i < N; ++i) {
+        const float gx = nrm(gen);
+        const float gy = nrm(gen);
+        const float gz = nrm(gen);
+        const float radius = std::cbrt(uni(gen));
+        const float u = uni(gen);
+        const float scale = radius / std::sqrt(gx * gx + gy * gy + gz * gz);
+        float* v = out + 3 * (size_t)i;
+        v[0] = gx * scale; v[1] = gy * scale; v[2] = gz * scale;
+        out[3 * (size_t)N + i] = u;
+    }
+    return RT_OK;
+}
+
+int rt_set_random_table(rt_ctx* c, const float* table, uint32_t n_floats) {
+    if (!c || !table) return fail(RT_ERR_INVALID, "rt_set_random_table: null argument");
+    if (n_floats != RT_RANDOM_TABLE_FLOATS) return fail(RT_ERR_INVALID, "rt_set_random_table: expected %u floats", RT_RANDOM_TABLE_FLOATS);
+    Guard g(c);
+    if (!c->d_table) CU(cudaMalloc(&c->d_table, (size_t)n_floats * sizeof(float)));
+    CU(cudaMemcpyAsync(c->d_table, table, (size_t)n_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_set_params(rt_ctx* c, const rt_params* p) {
+    if (!c || !p) return fail(RT_ERR_INVALID, "rt_set_params: null argument");
+    if (p->max_depth == 0) return fail(RT_ERR_INVALID, "max_depth must be >= 1");
+    if (p->rng_mode > 1 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
+    c->prm = *p;
+    return RT_OK;
+}
+int rt_get_params(rt_ctx* c, rt_params* p) {
+    if (!c || !p) return fail(RT_ERR_INVALID, "rt_get_params: null argument");
+    *p = c->prm;
+    return RT_OK;
+}
+
+static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, uint32_t accum_mode) {
+    if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
+    if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
+    if (c->prm.rng_mode == RT_RNG_TABLE && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
+    if (n == 0) return RT_OK;
+    Guard g(c);
+    TraceLaunch L{};
+    L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
+    std::memcpy(L.cam, cam, 12 * sizeof(float));
+    L.W = c->W; L.H = c->H; L.first = first; L.n = n; L.depth = c->prm.max_depth;
+    L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
+    L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
+    L.rays = c->d_rays;
+    CU(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    unsigned long long rays = 0;
+    CU(cudaMemcpyAsync(&rays, c->d_rays, sizeof rays, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    float ms = 0.0f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.ms_last = ms;
+    c->stats.rays_last = rays;
+    c->stats.rays_total += rays;
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
+int rt_render(rt_ctx* c, const float cam[12]) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    c->stats.rays_total = 0;
+    int r = do_render(c, cam, 0u, 1u, RT_ACCUM_REFERENCE);
+    if (r == RT_OK) { c->sample_counter = 0; c->stats.samples_done = 1; }
+    return r;
+}
+int rt_render_again(rt_ctx* c, const float cam[12]) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    int r = do_render(c, cam, c->sample_counter + 1u, 1u, RT_ACCUM_REFERENCE);
+    if (r == RT_OK) { c->sample_counter += 1; c->stats.samples_done = c->sample_counter + 1; }
+    return r;
+}
+int rt_render_samples(rt_ctx* c, const float cam[12], uint32_t first, uint32_t n, uint32_t accum_mode) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (accum_mode > 1) return fail(RT_ERR_INVALID, "bad accum_mode");
+    if (accum_mode == RT_ACCUM_REFERENCE && first == 0) c->stats.rays_total = 0;
+    int r = do_render(c, cam, first, n, accum_mode);
+    if (r == RT_OK && n) {
+        if (accum_mode == RT_ACCUM_REFERENCE) { c->sample_counter = first + n - 1; c->stats.samples_done = first + n; }
+        else c->stats.samples_done += n;
+    }
+    return r;
+}
+int rt_clear_accum(rt_ctx* c) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    Guard g(c);
+    CU(cudaMemsetAsync(c->d_accum, 0, (size_t)c->W * c->H * sizeof(float4), c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.samples_done = 0; c->stats.rays_total = 0;
+    return RT_OK;
+}
+int rt_finalize(rt_ctx* c, uint32_t spp) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize: spp must be > 0");
+    Guard g(c);
+    CU(launch_finalize(c->d_accum, c->d_image, c->W * c->H, spp, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
+int rt_read_image(rt_ctx* c, float* rgba) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_read_image: null argument");
+    Guard g(c);
+    CU(cudaMemcpyAsync(rgba, c->d_image, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_read_accum(rt_ctx* c, float* rgba) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_read_accum: null argument");
+    Guard g(c);
+    CU(cudaMemcpyAsync(rgba, c->d_accum, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_get_stats(rt_ctx* c, rt_stats* s) {
+    if (!c || !s) return fail(RT_ERR_INVALID, "rt_get_stats: null argument");
+    *s = c->stats;
+    return RT_OK;
+}
+int rt_accum_device_ptr(rt_ctx* c, void** p, size_t* bytes) {
+    if (!c || !p) return fail(RT_ERR_INVALID, "null argument");
+    *p = c->d_accum;
+    if (bytes) *bytes = (size_t)c->W * c->H * sizeof(float4);
+    return RT_OK;
+}
+int rt_image_device_ptr(rt_ctx* c, void** p, size_t* bytes) {
+    if (!c || !p) return fail(RT_ERR_INVALID, "null argument");
+    *p = c->d_image;
+    if (bytes) *bytes = (size_t)c->W * c->H * sizeof(float4);
+    return RT_OK;
+}
+int rt_set_accum_device_buffer(rt_ctx* c, void* p, size_t bytes) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (!p) { c->d_accum = c->d_accum_own; return RT_OK; }
+    if (bytes < (size_t)c->W * c->H * sizeof(float4)) return fail(RT_ERR_INVALID, "accumulation buffer too small");
+    if (((uintptr_t)p & 15u) != 0) return fail(RT_ERR_INVALID, "accumulation buffer must be 16-byte aligned");
+    c->d_accum = (float4*)p;
+    return RT_OK;
+}
+
+// ---- probes ------------------------------------------------------------------------------------
+extern "C++" {
+namespace {
+struct Scratch {   // RAII device scratch for the probe calls
+    std::vector<void*> ptrs;
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    template <class T> cudaError_t alloc(T** p, size_t n) {
+        cudaError_t e = cudaMalloc((void**)p, (n ? n : 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(*p);
+        return e;
+    }
+};
+ProbeLaunch base_probe(const rt_ctx* c) {
+    ProbeLaunch L{};
+    L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
+    L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth;
+    L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.mesh_mode = c->prm.mesh_mode;
+    return L;
+}
+}  // namespace
+}  // extern "C++"
+
+int rt_read_primary_ids(rt_ctx* c, const float cam[12], uint32_t* ids, float* t) {
+    if (!c || !cam) return fail(RT_ERR_INVALID, "rt_read_primary_ids: null argument");
+    if (!c->have_scene) return fail(RT_ERR_STATE, "no scene uploaded");
+    Guard g(c);
+    const size_t n = (size_t)c->W * c->H;
+    Scratch s;
+    ProbeLaunch L = base_probe(c);
+    std::memcpy(L.cam, cam, 12 * sizeof(float));
+    L.n = (uint32_t)n;
+    CU(s.alloc(&L.out_id, n));
+    CU(s.alloc(&L.out_t, n));
+    CU(c->prm.arith == RT_ARITH_STRICT ? launch_probe_hits_strict(L, c->stream) : launch_probe_hits_fast(L, c->stream));
+    if (ids) CU(cudaMemcpyAsync(ids, L.out_id, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (t) CU(cudaMemcpyAsync(t, L.out_t, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
+int rt_trace_rays(rt_ctx* c, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t) {
+    if (!c || !rays6) return fail(RT_ERR_INVALID, "rt_trace_rays: null argument");
+    if (!c->have_scene) return fail(RT_ERR_STATE, "no scene uploaded");
+    if (n == 0) return RT_OK;
+    Guard g(c);
+    Scratch s;
+    ProbeLaunch L = base_probe(c);
+    float* d_rays6 = nullptr;
+    CU(s.alloc(&d_rays6, (size_t)n * 6));
+    CU(cudaMemcpyAsync(d_rays6, rays6, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream));
+    L.rays6 = d_rays6; L.n = n;
+    CU(s.alloc(&L.out_id, n));
+    CU(s.alloc(&L.out_t, n));
+    CU(c->prm.arith == RT_ARITH_STRICT ? launch_probe_hits_strict(L, c->stream) : launch_probe_hits_fast(L, c->stream));
+    if (out_id) CU(cudaMemcpyAsync(out_id, L.out_id, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_t) CU(cudaMemcpyAsync(out_t, L.out_t, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
+int rt_bounce_rays(rt_ctx* c, float* rays6, uint32_t n, const uint32_t* sample, const uint32_t* bounce,
+                   const uint32_t* gx, const uint32_t* gy, float* col3, uint8_t* ended) {
+    if (!c || !rays6 || !sample || !bounce || !gx || !gy || !col3 || !ended) return fail(RT_ERR_INVALID, "rt_bounce_rays: null argument");
+    if (!c->have_scene) return fail(RT_ERR_STATE, "no scene uploaded");
+    if (c->prm.rng_mode == RT_RNG_TABLE && !c->d_table) return fail(RT_ERR_STATE, "table RNG selected but no random table set");
+    if (n == 0) return RT_OK;
+    Guard g(c);
+    Scratch s;
+    ProbeLaunch L = base_probe(c);
+    float *d_in = nullptr, *d_out = nullptr, *d_col = nullptr;
+    uint32_t *d_s = nullptr, *d_b = nullptr, *d_x = nullptr, *d_y = nullptr;
+    uint8_t* d_e = nullptr;
+    CU(s.alloc(&d_in, (size_t)n * 6)); CU(s.alloc(&d_out, (size_t)n * 6)); CU(s.alloc(&d_col, (size_t)n * 3));
+    CU(s.alloc(&d_s, n)); CU(s.alloc(&d_b, n)); CU(s.alloc(&d_x, n)); CU(s.alloc(&d_y, n)); CU(s.alloc(&d_e, n));
+    CU(cudaMemcpyAsync(d_in, rays6, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_s, sample, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_b, bounce, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_x, gx, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_y, gy, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    L.rays6 = d_in; L.rays6_out = d_out; L.n = n; L.sample = d_s; L.bounce = d_b; L.gx = d_x; L.gy = d_y;
+    L.col3 = d_col; L.ended = d_e;
+    CU(c->prm.arith == RT_ARITH_STRICT ? launch_probe_bounce_strict(L, c->stream) : launch_probe_bounce_fast(L, c->stream));
+    CU(cudaMemcpyAsync(rays6, d_out, (size_t)n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(col3, d_col, (size_t)n * 12, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(ended, d_e, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(int device, double* gslots_per_s, double* sm_clock_mhz) {
+    if (!gslots_per_s) return fail(RT_ERR_INVALID, "rt_measure_fp32_peak: null output");
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev)
+        return fail(RT_ERR_CUDA, "rt_measure_fp32_peak: no such CUDA device");
+    int prev = 0;
+    CU(cudaGetDevice(&prev));
+    CU(cudaSetDevice(device));
+    int sms = 0, khz = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    CU(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device));
+    float* sink = nullptr;
+    CU(cudaMalloc(&sink, 4));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    const int blocks = sms * 8, threads = 256, iters = 4096;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(e0, 0));
+        CU(launch_fp32_peak(sink, iters, blocks, threads, 0));
+        CU(cudaEventRecord(e1, 0));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        const double slots = (double)blocks * threads * (double)iters * 8.0 * 16.0;
+        if (rep > 0) best = std::fmax(best, slots / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    cudaSetDevice(prev);
+    *gslots_per_s = best;
+    if (sm_clock_mhz) *sm_clock_mhz = khz / 1000.0;
+    return RT_OK;
+}
+
+}  // extern "C"

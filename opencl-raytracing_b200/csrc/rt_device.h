@@ -1,0 +1,101 @@
+// csrc/rt_device.h — device-side scene layout and launch parameters shared by the host layer and the kernels.
+//
+// The reference keeps arrays of structs in global memory and chases pointers per primitive
+// (kernels/raytracer.cl:74-103).  Here the intersection data is a flat structure-of-float4 "test stream"
+// that every block stages into shared memory once and then reads with warp-uniform (broadcast) LDS.128;
+// data only needed for the ONE winning primitive of a ray ("shade" arrays) stays in global memory.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace rtb {
+
+// ---- test stream (float4 units), in hitScene order: spheres, planes, lenses, then mesh instances -------------
+//   sphere   : 1 x float4  (c.x, c.y, c.z, r*r)
+//   plane    : 2 x float4  (p.xyz, -) (n.xyz, -)
+//   lens     : 2 x float4  (p1.xyz, r1*r1) (p2.xyz, r2*r2)
+//   triangle : 3 x float4  (A.xyz, e1.x) (e1.y, e1.z, e2.x, e2.y) (e2.z, n.x, n.y, n.z)
+//              e1 = B - A, e2 = C - A, n = normalize(cross(e1, e2)) precomputed on the host with the same
+//              single-rounded float operations the reference performs per ray (kernels/raytracer.cl:264-265,285)
+struct alignas(16) MeshInst {   // one per (model, mesh) pair in hitModel order; read on the device as 3 x uint4
+    uint32_t tri_first;    // index into the triangle part of the stream
+    uint32_t tri_count;
+    uint32_t face_id_base; // reference-global face number of the first triangle (index_anchor / 3)
+    uint32_t mat_id;       // the owning model's material (kernels/raytracer.cl:314)
+    uint32_t texture_id;   // kernels/raytracer.cl:296
+    uint32_t _pad[3];
+    float    bound[4];     // conservative bounding sphere (c.xyz, r) of the mesh instance
+};
+
+struct DevScene {
+    const float4* stream;      // test stream in global memory (staged to shared memory per block)
+    uint32_t stream_f4;        // number of float4 in the stream
+    uint32_t n_sph, n_pla, n_len, n_tri, n_mesh;
+    uint32_t off_pla, off_len, off_tri;   // float4 offsets of each section
+    const MeshInst* mesh;      // n_mesh
+    // shade arrays (global)
+    const float4* sph_shade;   // (c.xyz, r)
+    const uint32_t* sph_mat;
+    const float4* pla_normal;  // (n.xyz, -)
+    const uint32_t* pla_mat;
+    const float4* len_shade;   // 2 per lens: (p1.xyz, r1) (p2.xyz, r2)
+    const uint32_t* len_mat;
+    const float2* tri_uv;      // 3 per triangle (uvA, uvB, uvC)
+    const uint32_t* tri_mesh;  // mesh instance of each triangle
+    const float4* mat;         // 2 per material: (type as int bits, extra, -, -) (color.rgb, -)
+    uint32_t n_mat;
+};
+
+struct DevTexture {
+    const float4* texels;      // [layer][row][col] RGBA f32
+    int w, h, layers;
+};
+
+struct TraceLaunch {
+    DevScene sc;
+    DevTexture tex;
+    const float* table;        // 400 000 floats (table RNG) or nullptr
+    float cam[12];             // src/camera.cpp:94-118
+    int W, H;
+    uint32_t first, n;         // samples [first, first + n)
+    uint32_t depth;
+    uint32_t rng_mode, seed, accum_mode, mesh_mode;
+    float4* target;            // image (reference chain) or accumulation buffer (sum)
+    unsigned long long* rays;  // device counter
+};
+
+struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays
+    DevScene sc;
+    DevTexture tex;
+    const float* table;
+    float cam[12];
+    int W, H;
+    uint32_t depth, rng_mode, seed, mesh_mode;
+    const float* rays6;        // n x 6 (nullptr -> primary rays of the W x H frame)
+    float* rays6_out;
+    uint32_t n;
+    uint32_t* out_id;
+    float* out_t;
+    const uint32_t *sample, *bounce, *gx, *gy;
+    float* col3;
+    uint8_t* ended;
+};
+
+static_assert(sizeof(MeshInst) == 48, "MeshInst is three 16-byte words");
+
+constexpr uint32_t kIdMiss = 0xFFFFFFFFu;
+constexpr uint32_t kKindSphere = 1u, kKindPlane = 2u, kKindLens = 3u, kKindTriangle = 4u;
+constexpr int kTraceThreads = 128;          // 4 warps, each an 8 x 4 pixel tile
+constexpr size_t kMaxStagedBytes = 160 * 1024;
+
+// launchers, one set per arithmetic flavour (rt_kernels_strict.cu / rt_kernels_fast.cu)
+cudaError_t launch_trace_strict(const TraceLaunch& p, cudaStream_t s);
+cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s);
+cudaError_t launch_probe_hits_strict(const ProbeLaunch& p, cudaStream_t s);
+cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s);
+cudaError_t launch_probe_bounce_strict(const ProbeLaunch& p, cudaStream_t s);
+cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s);
+cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);
+cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t s);
+
+}  // namespace rtb

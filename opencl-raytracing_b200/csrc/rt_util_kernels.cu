@@ -1,0 +1,44 @@
+// csrc/rt_util_kernels.cu — finalize (tail of kernels/raytracer.cl:509,531 on a summed buffer) and the
+// FP32-issue microbenchmark that supplies the roofline denominator MEASURED_PEAKS.json lacks.
+#include "rt_device.h"
+
+namespace rtb {
+
+__global__ void k_finalize(const float4* __restrict__ accum, float4* __restrict__ image, int n, float inv_spp) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = accum[i];
+    image[i] = make_float4(sqrtf(a.x * inv_spp), sqrtf(a.y * inv_spp), sqrtf(a.z * inv_spp), 1.0f);
+}
+
+cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s) {
+    if (n_pixels <= 0) return cudaSuccess;
+    k_finalize<<<(n_pixels + 255) / 256, 256, 0, s>>>(accum, image, n_pixels, 1.0f / (float)spp);
+    return cudaGetLastError();
+}
+
+// 16 independent FFMA chains per thread; 2 flops / 1 issue slot per FFMA per lane.
+__global__ void __launch_bounds__(256) k_fp32_peak(float* sink, int iters) {
+    float a[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) a[j] = (float)(threadIdx.x + j) * 1e-3f;
+    const float m = 1.000001f, c = 1e-7f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a[j] = fmaf(a[j], m, c);
+        }
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s += a[j];
+    if (s == 123.456f) sink[0] = s;   // never true; keeps the chains alive
+}
+
+cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t s) {
+    k_fp32_peak<<<blocks, threads, 0, s>>>(sink, iters);
+    return cudaGetLastError();
+}
+
+}  // namespace rtb

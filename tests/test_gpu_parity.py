@@ -1,0 +1,242 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C ABI (rtb200 is a
+ctypes binding of include/rt_capi.h) and is checked against the oracle on the same seeded inputs.
+
+Bars (stated here, repeated in DESIGN.md):
+  STRICT arithmetic  bit-exact: image bits, ray counts, primary ids and t, single-bounce outputs.
+                     (A dielectric pow() rounding flip is possible with probability ~1e-8 per bounce; the
+                      image tests allow <= 3 differing pixels per frame for that single reason.)
+  FAST arithmetic    identical primary-hit ids; single-bounce outputs within 2e-4 absolute for
+                     non-chaotic (non-table-hashed) results; image RMSE(gamma) vs oracle <= 0.03 at 16 spp
+                     (the reference's own FMA-on/off difference is 0.022) and mean difference <= 2e-3.
+  COUNTER RNG        strict arithmetic is bit-exact against the oracle's counter mode; statistically equal
+                     to table mode: 16x16 block-mean RMSE <= 2x the table seed-to-seed value.
+"""
+import numpy as np
+import pytest
+
+import oracle_py as op
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def rt():
+    import rtb200
+    return rtb200
+
+
+def make_ctx(rt, scenes, name, W, H, table, **params):
+    arr, tex = scenes[name]
+    ctx = rt.Context(W, H)
+    ctx.upload_textures(tex)
+    ctx.upload_scene(arr)
+    ctx.set_random_table(table)
+    ctx.set_params(**params)
+    return ctx
+
+
+def n_diff_pixels(a, b):
+    return int((bits(a[..., :3]) != bits(b[..., :3])).any(-1).sum())
+
+
+@pytest.mark.parametrize("name,W,H,spp,depth", [("default", 800, 600, 16, 8), ("default", 320, 200, 8, 30),
+                                               ("c3", 480, 270, 8, 30), ("default", 101, 67, 3, 2)])
+def test_strict_image_bit_exact(rt, port, scenes, table, name, W, H, spp, depth):
+    """BASELINE config C1 (800x600, 16 spp, depth 8) and friends: strict CUDA == oracle, bit for bit."""
+    from rtb200 import fixtures as fx
+    arr, tex = scenes[name]
+    cam = fx.camera(60, W / H)
+    want, rays_want, _ = port.render(op.make_desc(arr), tex, cam, table, W, H, 0, spp, port.params(max_depth=depth))
+    with make_ctx(rt, scenes, name, W, H, table, max_depth=depth, arith=rt.ARITH_STRICT) as ctx:
+        # (a) the reference's own call sequence: render() then renderAgain() x (spp-1)
+        ctx.render(cam)
+        rays = ctx.stats().rays_last
+        for _ in range(spp - 1):
+            ctx.render_again(cam)
+            rays += ctx.stats().rays_last
+        got = ctx.read_image()
+        assert n_diff_pixels(got, want) <= 3
+        assert abs(int(rays) - int(rays_want)) <= 60
+        assert ctx.stats().rays_total == rays and ctx.stats().samples_done == spp
+        assert np.all(got[..., 3] == 1.0)
+        # (b) all samples in one launch: identical bits to the sequential calls
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        got2 = ctx.read_image()
+        assert np.array_equal(bits(got2), bits(got))
+        assert ctx.stats().rays_last == rays
+        # (c) split launches continue the chain
+        ctx.render_samples(cam, 0, spp // 2, rt.ACCUM_REFERENCE)
+        ctx.render_samples(cam, spp // 2, spp - spp // 2, rt.ACCUM_REFERENCE)
+        assert np.array_equal(bits(ctx.read_image()), bits(got))
+
+
+@pytest.mark.parametrize("name", ["default", "c3"])
+def test_golden_fixture_images(rt, scenes, golden, table, name):
+    """Against the committed outputs of the reference kernel build (no oracle code involved at run time)."""
+    g = golden[name]
+    W, H, cam = int(g["W"]), int(g["H"]), g["cam"]
+    with make_ctx(rt, scenes, name, W, H, table, max_depth=30, arith=rt.ARITH_STRICT) as ctx:
+        ctx.render(cam)
+        assert n_diff_pixels(ctx.read_image(), g["image_1spp"]) <= 1
+        assert abs(int(ctx.stats().rays_last) - int(g["rays_1spp"])) <= 20
+        for _ in range(3):
+            ctx.render_again(cam)
+        assert n_diff_pixels(ctx.read_image(), g["image_4spp"]) <= 2
+        ids, ts = ctx.primary_ids(cam)
+        assert np.array_equal(ids, g["ids"]) and np.array_equal(bits(ts), bits(g["ts"]))
+        ctx.set_params(max_depth=8, arith=rt.ARITH_STRICT)
+        ctx.render_samples(cam, 0, 4, rt.ACCUM_REFERENCE)
+        assert n_diff_pixels(ctx.read_image(), g["image_4spp_depth8"]) <= 2
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+@pytest.mark.parametrize("name,W,H", [("default", 800, 600), ("default", 1920, 1080), ("c3", 1920, 1080), ("c3", 480, 270)])
+def test_primary_ids_identical(rt, port, scenes, golden, table, name, W, H, arith):
+    from rtb200 import fixtures as fx
+    arr, _ = scenes[name]
+    cam = fx.camera(60, W / H)
+    want_ids, want_t = port.primary_ids(op.make_desc(arr), cam, W, H)
+    with make_ctx(rt, scenes, name, W, H, table, arith=getattr(rt, "ARITH_" + arith.upper())) as ctx:
+        ids, ts = ctx.primary_ids(cam)
+    assert int((ids != want_ids).sum()) == 0
+    if arith == "strict":
+        assert np.array_equal(bits(ts), bits(want_t))
+    else:
+        assert np.abs(ts - want_t).max() <= 1e-3 * 1000.0 * 1e-3 + 1e-3
+    if (W, H) == (int(golden[name]["big_W"]), int(golden[name]["big_H"])):
+        assert np.array_equal(ids, golden[name]["big_ids"])
+
+
+@pytest.mark.parametrize("name", ["default", "c3"])
+def test_single_bounce_vectors(rt, scenes, golden, table, name):
+    """Recorded (ray, seed, pixel) -> (new ray, throughput) tuples of the reference kernel: immune to chaos."""
+    g = golden[name]
+    meta = g["bounce_meta"]
+    with make_ctx(rt, scenes, name, int(g["W"]), int(g["H"]), table, arith=rt.ARITH_STRICT) as ctx:
+        r, col, ended = ctx.bounce_rays(g["bounce_in"], meta[:, 0] + meta[:, 1], 0, meta[:, 2], meta[:, 3])
+        assert np.array_equal(bits(r), bits(g["bounce_out"]))
+        assert np.array_equal(bits(col), bits(g["bounce_col"]))
+        ctx.set_params(arith=rt.ARITH_FAST)
+        r2, col2, _ = ctx.bounce_rays(g["bounce_in"], meta[:, 0] + meta[:, 1], 0, meta[:, 2], meta[:, 3])
+    # fast arithmetic: origins (hit points) agree closely; directions of diffuse bounces depend on the table
+    # hash of the direction (chaotic), so compare those only where the strict direction was reproduced closely
+    assert np.abs(r2[:, :3] - g["bounce_out"][:, :3]).max() < 2e-3
+    close = np.abs(r2[:, 3:] - g["bounce_out"][:, 3:]).max(1) < 1e-3
+    assert close.mean() > 0.9
+    assert np.abs(col2[close] - g["bounce_col"][close]).max() < 1e-3
+
+
+def test_fast_image_statistics(rt, port, scenes, table):
+    """C1: fast arithmetic vs oracle at 16 spp: RMSE(gamma) <= 0.03, mean difference <= 2e-3, rays within 0.1 %."""
+    from rtb200 import fixtures as fx
+    W, H, spp, depth = 800, 600, 16, 8
+    arr, tex = scenes["default"]
+    cam = fx.camera(60, W / H)
+    want, rays_want, _ = port.render(op.make_desc(arr), tex, cam, table, W, H, 0, spp, port.params(max_depth=depth))
+    with make_ctx(rt, scenes, "default", W, H, table, max_depth=depth, arith=rt.ARITH_FAST) as ctx:
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        got = ctx.read_image()
+        rays = ctx.stats().rays_last
+        # linear-sum path gives the same picture up to float summation order
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+        ctx.finalize(spp)
+        got_sum = ctx.read_image()
+    d = got[..., :3] - want[..., :3]
+    assert np.sqrt((d * d).mean()) <= 0.03
+    assert abs(float(got[..., :3].mean()) - float(want[..., :3].mean())) <= 2e-3
+    assert abs(int(rays) - int(rays_want)) <= 1e-3 * rays_want
+    assert np.abs(got_sum[..., :3] - got[..., :3]).max() < 1e-4
+
+
+def block_means(img, b=16):
+    H, W = img.shape[:2]
+    lin = img[: H // b * b, : W // b * b, :3].astype(np.float64) ** 2      # linear radiance
+    return lin.reshape(H // b, b, W // b, b, 3).mean((1, 3))
+
+
+def test_counter_rng_strict_bit_exact_and_same_law(rt, port, scenes, table):
+    from rtb200 import fixtures as fx
+    W, H, spp = 320, 240, 64
+    arr, tex = scenes["default"]
+    d = op.make_desc(arr)
+    cam = fx.camera(60, W / H)
+    want, rays_want, _ = port.render(d, tex, cam, None, W, H, 0, spp, port.params(max_depth=30, rng_mode=op.RNG_COUNTER, seed=77))
+    with make_ctx(rt, scenes, "default", W, H, table, max_depth=30, arith=rt.ARITH_STRICT, rng_mode=rt.RNG_COUNTER, seed=77) as ctx:
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        got = ctx.read_image()
+        assert n_diff_pixels(got, want) <= 3
+        assert abs(int(ctx.stats().rays_last) - int(rays_want)) <= 60
+        ctx.set_params(max_depth=30, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER, seed=78)
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        fast_c = ctx.read_image()
+    # the law: counter-mode block means agree with table-mode block means as well as two table seeds agree
+    t_a, _, _ = port.render(d, tex, cam, table, W, H, 0, spp, port.params(max_depth=30))
+    t_b, _, _ = port.render(d, tex, cam, port.make_table(999), W, H, 0, spp, port.params(max_depth=30))
+    noise = np.sqrt(((block_means(t_a) - block_means(t_b)) ** 2).mean())
+    for img in (got, fast_c):
+        err = np.sqrt(((block_means(img) - block_means(t_a)) ** 2).mean())
+        assert err <= 2.0 * noise, (err, noise)
+        assert abs(float((img[..., :3] ** 2).mean()) - float((t_a[..., :3] ** 2).mean())) <= 0.004
+
+
+def test_sample_split_sums_to_whole(rt, scenes, table):
+    """What the multi-GPU split relies on: disjoint global sample ranges accumulate to the single-launch sum."""
+    from rtb200 import fixtures as fx
+    W, H = 256, 128
+    cam = fx.camera(60, W / H)
+    with make_ctx(rt, scenes, "default", W, H, table, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER, seed=5) as ctx:
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, 12, rt.ACCUM_SUM)
+        whole = ctx.read_accum()
+        parts = np.zeros_like(whole)
+        for first, n in ((0, 3), (3, 3), (6, 6)):
+            ctx.clear_accum()
+            ctx.render_samples(cam, first, n, rt.ACCUM_SUM)
+            parts += ctx.read_accum()
+    assert np.all(whole[..., 3] == 12) and np.all(parts[..., 3] == 12)
+    assert np.abs(parts - whole).max() <= 1e-5 * max(1.0, float(np.abs(whole).max()))
+
+
+def test_random_rays_match_oracle(rt, port, scenes, table):
+    rng = np.random.RandomState(11)
+    n = 20000
+    o = rng.uniform(-6, 6, (n, 3)).astype(np.float32)
+    v = rng.normal(size=(n, 3))
+    v = (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+    rays = np.concatenate([o, v], 1)
+    for name in ("default", "c3"):
+        arr, _ = scenes[name]
+        d = op.make_desc(arr)
+        want = [port.intersect(d, rays[i, :3], rays[i, 3:]) for i in range(0, n, 10)]
+        want_id = np.array([h.id for _, h in want], np.uint32)
+        want_t = np.array([h.t for _, h in want], np.float32)
+        with make_ctx(rt, scenes, name, 64, 64, table, arith=rt.ARITH_STRICT) as ctx:
+            ids, ts = ctx.trace_rays(rays[::10])
+            assert np.array_equal(ids, want_id) and np.array_equal(bits(ts), bits(want_t))
+            ctx.set_params(arith=rt.ARITH_FAST)
+            ids_f, _ = ctx.trace_rays(rays[::10])
+            assert (ids_f != want_id).mean() < 1e-3
+
+
+def test_errors_are_reported_not_fatal(rt, scenes, table):
+    arr, tex = scenes["default"]
+    from rtb200 import fixtures as fx
+    ctx = rt.Context(32, 32)
+    with pytest.raises(rt.RtError):
+        ctx.render(fx.camera(60, 1.0))               # no scene yet
+    bad = dict(arr)
+    sph = arr["spheres"].copy()
+    sph[0, 20:24] = np.frombuffer(np.uint32(99).tobytes(), np.uint8)   # material id out of range
+    bad["spheres"] = sph
+    with pytest.raises(rt.RtError) as e:
+        ctx.upload_scene(bad)
+    assert "material" in str(e.value)
+    ctx.upload_scene(arr)
+    with pytest.raises(rt.RtError):
+        ctx.render(fx.camera(60, 1.0))               # table mode without a table
+    ctx.close()
