@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: Mrays/s of the path-tracing hot path on BASELINE.json's config C2
+(default scene, 1920x1080, 1024 spp, depth 30) on N B200s, beside the reference kernel on the host cores.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one full pass of the hot path over the workload: every pixel x every sample of the job.
+ray = one nearest-hit query (path segment), counted by the kernel itself.
+N > 1: the job's samples are split across ranks (global sample indices, so the picture does not depend on N),
+each rank accumulates a private linear-sum buffer, one NCCL reduce (torch.distributed) sums them on rank 0,
+rank 0 finalizes.  `scaling` is therefore "strong".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "opencl-raytracing_b200"))
+
+W, H, SPP, DEPTH = 1920, 1080, 1024, 30
+TABLE_SEED = 12345
+SLOTS_PER_RAY = 867.0   # measured FP32 issue slots per ray of the reference algorithm, default scene
+METRIC = "Mrays/s at 1080p per scene, 1/2/4/8 B200, vs reference OpenCL on host CPU"
+WORKLOAD = "C2: default scene (8 spheres, 1 plane, 1 lens, 2 textured cubes = 24 triangles), 1920x1080, 1024 spp, max depth 30"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--spp", type=int, default=SPP)
+    ap.add_argument("--arith", default="fast", choices=["fast", "strict"])
+    ap.add_argument("--rng", default="counter", choices=["counter", "table"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_inputs():
+    import rtb200
+    from rtb200 import fixtures as fx
+    arr, tex8 = fx.default_scene()
+    tex = fx.textures_to_float(tex8)
+    cam = fx.camera(60, W / H)
+    table = rtb200.make_random_table(TABLE_SEED)
+    return arr, tex, cam, table
+
+
+def cpu_reference_rate(spp_per_step, steps, warmup, first=0):
+    """The reference's own kernel text compiled as C++ (oracle/_ref/libref_fast.so), all host threads, one
+    NDRange-equivalent pass per sample like render()/renderAgain().  Returns (Mrays/s, cores, kind, sample)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import oracle_py as op
+    arr, tex, cam, table = load_inputs()
+    cores = os.cpu_count() or 1
+    try:
+        R, kind = op.RefOracle("fast"), "reference"
+        def run(first, n, img):
+            _, rays, secs = R.render(d, tex, cam, table, W, H, first, n, depth=DEPTH, threads=cores, image=img)
+            return rays, secs
+    except (FileNotFoundError, OSError):
+        P, kind = op.PortOracle(), "port"
+        def run(first, n, img):
+            _, rays, secs = P.render(d, tex, cam, table, W, H, first, n, P.params(max_depth=DEPTH, threads=cores), image=img)
+            return rays, secs
+    d = op.make_desc(arr)
+    img = np.zeros((H, W, 4), np.float32)
+    k = first
+    for _ in range(warmup):
+        run(k, spp_per_step, img); k += spp_per_step
+    rays_t, secs_t, per_step = 0, 0.0, []
+    for _ in range(steps):
+        r, s = run(k, spp_per_step, img); k += spp_per_step
+        rays_t += r; secs_t += s; per_step.append(s)
+    return rays_t / secs_t / 1e6, cores, kind, rays_t, secs_t, per_step
+
+
+def main_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    spp_step = 2
+    rate, cores, kind, rays, secs, per = cpu_reference_rate(spp_step, a.steps, a.warmup)
+    sample = "%dx%d, %d spp per step (one pass per sample), depth %d, %d host threads" % (W, H, spp_step, DEPTH, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(rate, 3), "unit": "Mrays/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1e3 * secs / max(a.steps, 1), 3),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": round(rate, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main_b200(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import rtb200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    arith = rtb200.ARITH_FAST if a.arith == "fast" else rtb200.ARITH_STRICT
+    rng = rtb200.RNG_COUNTER if a.rng == "counter" else rtb200.RNG_TABLE
+
+    arr, tex, cam, table = load_inputs()
+    ctx = rtb200.Context(W, H, local)
+    ctx.upload_textures(tex); ctx.upload_scene(arr); ctx.set_random_table(table)
+    ctx.set_params(max_depth=DEPTH, rng_mode=rng, seed=1, arith=arith)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+    spp = a.spp
+    first = rank * spp // world
+    n_mine = (rank + 1) * spp // world - first
+
+    peak_gslots, nominal_mhz = rtb200.measure_fp32_peak(local)
+
+    def step():
+        accum.zero_()
+        ctx.render_samples(cam, first, n_mine, rtb200.ACCUM_SUM)
+        rays = ctx.stats().rays_last
+        kms = ctx.stats().ms_last
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            ctx.finalize(spp)
+        return rays, kms
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        step(); flush.zero_()
+    launches0 = ctx.stats().kernel_launches
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    rays_steps, kernel_ms = [], []
+    for _ in range(a.steps):
+        r, kms = step()
+        rays_steps.append(r); kernel_ms.append(kms)
+        flush.zero_()
+    e1.record(stream)
+    sync_all()
+    elapsed_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ctx.stats().kernel_launches - launches0
+
+    t = torch.tensor([elapsed_ms, float(sum(rays_steps)), float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        elapsed_ms, rays_total, launches = tmax[0].item(), tsum[1].item(), int(tsum[2].item())
+    else:
+        rays_total = t[1].item()
+    value = rays_total / (elapsed_ms * 1e-3) / 1e6
+
+    # ---- end to end through the C ABI with HOST buffers: every step uploads scene, textures, table (pinned
+    # host memory -> device), renders, reduces, finalizes and reads the image back to the host.
+    img_host = np.empty((H, W, 4), np.float32)
+    tex_pinned = torch.from_numpy(tex).pin_memory()
+    table_pinned = torch.from_numpy(table).pin_memory()
+    h2d = tex_pinned.numel() * 4 + table_pinned.numel() * 4 + sum(v.nbytes for v in arr.values()) + 48
+    d2h = img_host.nbytes if rank == 0 else 0
+
+    def e2e_step():
+        ctx.upload_textures(tex_pinned.numpy()); ctx.upload_scene(arr); ctx.set_random_table(table_pinned.numpy())
+        r, _ = step()
+        if rank == 0:
+            ctx.read_image(img_host)
+        return r
+
+    e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    e2e_rays = 0
+    e2e_steps = max(1, min(a.steps, 3))
+    for _ in range(e2e_steps):
+        e2e_rays += e2e_step()
+    sync_all()
+    e2e_s = time.perf_counter() - t0
+    t2 = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        m = t2.clone(); dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        s = t2.clone(); dist.all_reduce(s, op=dist.ReduceOp.SUM)
+        e2e_s, e2e_rays = m[0].item(), s[1].item()
+    e2e_value = e2e_rays / e2e_s / 1e6
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        k_ms = sum(kernel_ms) / len(kernel_ms)
+        rays_launch = rays_steps[0]
+        achieved = SLOTS_PER_RAY * rays_launch / (k_ms * 1e-3) / 1e9
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        alg_bytes = 2.0 * W * H * 16          # accumulation buffer read + write, once per launch
+        out = {
+            "metric": METRIC, "value": round(value, 1), "unit": "Mrays/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": round(elapsed_ms / a.steps, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "spp_total": spp, "spp_per_gpu": n_mine, "arith": a.arith, "rng": a.rng,
+                       "parallelism": "spp-split x%d + 1 NCCL reduce" % world if world > 1 else "single GPU",
+                       "l2": "flushed between steps (256 MiB memset); inputs are < 40 MB, the kernel is issue bound",
+                       "rays_per_step": int(rays_total / a.steps)},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 1), "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                    "what": "rt_upload_textures + rt_upload_scene + rt_set_random_table from pinned host memory, "
+                            "rt_render_samples, reduce, rt_finalize, rt_read_image to host, every step"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "fp32_issue", "achieved": round(achieved, 1), "peak": round(peak_gslots, 1),
+                         "unit": "G lane-slots/s", "frac": round(achieved / peak_gslots, 4) if peak_gslots else None,
+                         "traffic": None, "kernel": "k_trace_%s" % a.arith, "kernel_ms": round(k_ms, 3),
+                         "slots_per_ray": SLOTS_PER_RAY, "rays_per_launch": int(rays_launch),
+                         "peak_source": "measured live: dependent-free FFMA loop on all SMs (rt_measure_fp32_peak); "
+                                        "MEASURED_PEAKS.json has no FP32 entry",
+                         "hbm": {"achieved_gbs": round(alg_bytes / (k_ms * 1e-3) / 1e9, 2), "peak_gbs": hbm_peak,
+                                 "note": "evidence only: 33 MB per launch, not the bound"}},
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            rate, cores, kind, rays, secs, _ = cpu_reference_rate(4, 4, 1)
+            out["cpu_baseline"] = {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind,
+                                   "sample": "%dx%d, 16 timed spp in 4 steps (one pass per sample), depth %d, %.1f s of CPU work"
+                                             % (W, H, DEPTH, secs)}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        main_reference(args)
+    else:
+        main_b200(args)

@@ -7,6 +7,7 @@
 #include "../../include/rt_capi.h"
 #include "rt_device.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -85,6 +86,7 @@ struct rt_ctx {
     DevBuf<MeshInst> b_mesh;
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
     uint32_t sample_counter = 0;
+    int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
     rt_stats stats{};
 };
 
@@ -157,6 +159,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     }
     const uint32_t off_tri = (uint32_t)stream.size();
     uint32_t n_tri = 0;
+    int64_t max_tex = -1;
     for (uint32_t mo = 0; mo < d->n_models; ++mo) {
         const HModel& M = models[mo];
         if (M.mat >= d->n_materials) return fail(RT_ERR_INVALID, "ERROR: MATERIAL OF ID: %u DOES NOT EXIST", M.mat);
@@ -164,8 +167,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         for (uint32_t k = 0; k < M.mesh_count; ++k) {
             const HMesh& me = meshes[M.mesh_anchor + k];
             if ((uint64_t)me.index_anchor + 3ull * me.face_count > d->n_indices) return fail(RT_ERR_INVALID, "mesh %u: index range out of bounds", M.mesh_anchor + k);
-            if (is_textured(M.mat) && me.texture_id >= (uint32_t)c->tex.layers && c->d_tex)
-                return fail(RT_ERR_INVALID, "mesh %u: texture %u does not exist", M.mesh_anchor + k, me.texture_id);
+            if (is_textured(M.mat)) max_tex = std::max<int64_t>(max_tex, me.texture_id);
             MeshInst mi{};
             mi.tri_first = n_tri; mi.tri_count = me.face_count; mi.face_id_base = me.index_anchor / 3u;
             mi.mat_id = M.mat; mi.texture_id = me.texture_id;
@@ -236,6 +238,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     sc.mat = c->b_mat.p; sc.n_mat = d->n_materials;
     c->stats.n_primitives = d->n_spheres + d->n_planes + d->n_lenses + n_tri;
     c->stats.bvh_nodes = 0;
+    c->max_texture_used = max_tex;
     c->have_scene = true;
     return RT_OK;
 }
@@ -378,6 +381,9 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
     if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
     if (c->prm.rng_mode == RT_RNG_TABLE && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
+    if (c->max_texture_used >= (int64_t)c->tex.layers)
+        return fail(RT_ERR_STATE, "render: a textured mesh uses texture %lld but only %d layer(s) are uploaded",
+                    (long long)c->max_texture_used, c->tex.layers);
     if (n == 0) return RT_OK;
     Guard g(c);
     TraceLaunch L{};
