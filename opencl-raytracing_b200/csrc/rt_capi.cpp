@@ -87,6 +87,11 @@ struct rt_ctx {
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
     uint32_t sample_counter = 0;
     int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
+    // fast arithmetic: Exact primary-hit ids of the current (scene, camera, mesh rule), see ensure_certified()
+    uint32_t* d_certify = nullptr;
+    float certify_cam[12] = {0};
+    uint32_t certify_mesh_mode = 0;
+    bool certify_valid = false;
     rt_stats stats{};
 };
 
@@ -215,7 +220,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         mat.push_back(make_float4(t, mats[i].extra, 0.0f, 0.0f));
         mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
     }
-    const size_t staged = (stream.size() + 3 * inst.size()) * sizeof(float4);
+    const size_t staged = (stream.size() + 3 * inst.size()) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
     if (staged > kMaxStagedBytes)
         return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); BVH path required", staged, kMaxStagedBytes);
 
@@ -239,7 +244,28 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     c->stats.n_primitives = d->n_spheres + d->n_planes + d->n_lenses + n_tri;
     c->stats.bvh_nodes = 0;
     c->max_texture_used = max_tex;
+    c->certify_valid = false;
     c->have_scene = true;
+    return RT_OK;
+}
+
+// Fast arithmetic certifies its primary hits: one Exact nearest-hit query per pixel, recomputed only when the
+// scene, the camera or the mesh rule changes.  The fast kernels compare their own primary id with it and fall
+// back to the Exact intersection on the (knife-edge) pixels where they differ.
+int ensure_certified(rt_ctx* c, const float* cam) {
+    if (c->certify_valid && c->certify_mesh_mode == c->prm.mesh_mode && std::memcmp(c->certify_cam, cam, 48) == 0) return RT_OK;
+    const size_t n = (size_t)c->W * c->H;
+    if (!c->d_certify) CU(cudaMalloc(&c->d_certify, n * sizeof(uint32_t)));
+    ProbeLaunch L{};
+    L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
+    std::memcpy(L.cam, cam, 48);
+    L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth; L.mesh_mode = c->prm.mesh_mode;
+    L.n = (uint32_t)n; L.out_id = c->d_certify;
+    CU(launch_probe_hits_strict(L, c->stream));
+    c->stats.kernel_launches += 1;
+    std::memcpy(c->certify_cam, cam, 48);
+    c->certify_mesh_mode = c->prm.mesh_mode;
+    c->certify_valid = true;
     return RT_OK;
 }
 
@@ -295,6 +321,7 @@ int rt_destroy(rt_ctx* c) {
     {
         Guard g(c);
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+        cudaFree(c->d_certify);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
         c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
@@ -393,6 +420,11 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
+    if (c->prm.arith == RT_ARITH_FAST) {
+        int r = ensure_certified(c, cam);
+        if (r != RT_OK) return r;
+        L.certify_id = c->d_certify;
+    }
     CU(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), c->stream));
     CU(cudaEventRecord(c->ev0, c->stream));
     CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
@@ -524,6 +556,11 @@ int rt_read_primary_ids(rt_ctx* c, const float cam[12], uint32_t* ids, float* t)
     L.n = (uint32_t)n;
     CU(s.alloc(&L.out_id, n));
     CU(s.alloc(&L.out_t, n));
+    if (c->prm.arith == RT_ARITH_FAST) {
+        int r = ensure_certified(c, cam);
+        if (r != RT_OK) return r;
+        L.certify_id = c->d_certify;
+    }
     CU(c->prm.arith == RT_ARITH_STRICT ? launch_probe_hits_strict(L, c->stream) : launch_probe_hits_fast(L, c->stream));
     if (ids) CU(cudaMemcpyAsync(ids, L.out_id, n * 4, cudaMemcpyDeviceToHost, c->stream));
     if (t) CU(cudaMemcpyAsync(t, L.out_t, n * 4, cudaMemcpyDeviceToHost, c->stream));

@@ -62,6 +62,7 @@ struct TraceLaunch {
     uint32_t rng_mode, seed, accum_mode, mesh_mode;
     float4* target;            // image (reference chain) or accumulation buffer (sum)
     unsigned long long* rays;  // device counter
+    const uint32_t* certify_id; // fast arithmetic: Exact primary-hit id per pixel (nullptr = no certification)
 };
 
 struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays
@@ -79,6 +80,7 @@ struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounc
     const uint32_t *sample, *bounce, *gx, *gy;
     float* col3;
     uint8_t* ended;
+    const uint32_t* certify_id; // fast arithmetic: Exact hit id per ray (nullptr = no certification)
 };
 
 static_assert(sizeof(MeshInst) == 48, "MeshInst is three 16-byte words");

@@ -1,18 +1,24 @@
-// csrc/rt_kernels_fast.cu — throughput arm.  Build flags (Makefile): -fmad=true -prec-div=false -prec-sqrt=false
-#define RT_STRICT 0
-#define RT_FLAVOUR fast
-#define RT_KERNEL_NAME(n) n##_fast
+// csrc/rt_kernels_fast.cu — the throughput arm: kernels instantiated with the Fused arithmetic policy
+// (FMA contraction, MUFU rcp/sqrt/rsqrt), primary hits certified against the Exact policy.
 #include "rt_kernels.cuh"
 
 namespace rtb {
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_fast(const __grid_constant__ TraceLaunch p) {
+    extern __shared__ float4 smem[];
+    trace_body<Fused>(p, smem);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {
+    extern __shared__ float4 smem[];
+    probe_hits_body<Fused>(p, smem);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_bounce_fast(const __grid_constant__ ProbeLaunch p) {
+    extern __shared__ float4 smem[];
+    probe_bounce_body<Fused>(p, smem);
+}
 cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s) {
     const size_t tiles = (size_t)((p.W + 7) / 8) * ((p.H + 3) / 4);
-    return fast::launch_staged(fast::k_trace_fast, p, tiles * 32, s);
+    return launch_staged(k_trace_fast, p, tiles * 32, s);
 }
-cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) {
-    return fast::launch_staged(fast::k_probe_hits_fast, p, p.n, s);
-}
-cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s) {
-    return fast::launch_staged(fast::k_probe_bounce_fast, p, p.n, s);
-}
+cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) { return launch_staged(k_probe_hits_fast, p, p.n, s); }
+cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s) { return launch_staged(k_probe_bounce_fast, p, p.n, s); }
 }  // namespace rtb
