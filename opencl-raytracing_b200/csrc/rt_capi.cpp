@@ -83,6 +83,7 @@ struct rt_ctx {
     DevBuf<float4> b_stream, b_sph_shade, b_pla_normal, b_len_shade, b_mat;
     DevBuf<uint32_t> b_sph_mat, b_pla_mat, b_len_mat, b_tri_mesh;
     DevBuf<float2> b_tri_uv;
+    DevBuf<float> b_tri_pd;
     DevBuf<MeshInst> b_mesh;
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
     uint32_t sample_counter = 0;
@@ -134,6 +135,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     std::vector<float4> stream, sph_shade, pla_normal, len_shade, mat;
     std::vector<uint32_t> sph_mat, pla_mat, len_mat, tri_mesh;
     std::vector<float2> tri_uv;
+    std::vector<float> tri_pd;
     std::vector<MeshInst> inst;
 
     for (uint32_t i = 0; i < d->n_spheres; ++i) {
@@ -197,6 +199,12 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
                 stream.push_back(make_float4(P[0][0], P[0][1], P[0][2], e1[0]));
                 stream.push_back(make_float4(e1[1], e1[2], e2[0], e2[1]));
                 stream.push_back(make_float4(e2[2], nx * inv, ny * inv, nz * inv));
+                {   // plane offset for the conservative front-side filter (not parity relevant: it only removes
+                    // triangles whose hit parameter would be negative); margin covers float rounding on the device
+                    const double nd[3] = {(double)(nx * inv), (double)(ny * inv), (double)(nz * inv)};
+                    const double pd = nd[0] * P[0][0] + nd[1] * P[0][1] + nd[2] * P[0][2];
+                    tri_pd.push_back((float)(pd - 4e-6 * (1.0 + std::fabs(pd))));
+                }
                 tri_uv.push_back(uv[0]); tri_uv.push_back(uv[1]); tri_uv.push_back(uv[2]);
                 tri_mesh.push_back((uint32_t)inst.size());
                 ++n_tri;
@@ -220,7 +228,8 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         mat.push_back(make_float4(t, mats[i].extra, 0.0f, 0.0f));
         mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
     }
-    const size_t staged = (stream.size() + 3 * inst.size()) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
+    while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
+    const size_t staged = (stream.size() + 3 * inst.size() + tri_pd.size() / 4) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
     if (staged > kMaxStagedBytes)
         return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); BVH path required", staged, kMaxStagedBytes);
 
@@ -229,6 +238,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     CU(c->b_pla_normal.upload(pla_normal, s)); CU(c->b_pla_mat.upload(pla_mat, s));
     CU(c->b_len_shade.upload(len_shade, s)); CU(c->b_len_mat.upload(len_mat, s));
     CU(c->b_tri_uv.upload(tri_uv, s));       CU(c->b_tri_mesh.upload(tri_mesh, s));
+    CU(c->b_tri_pd.upload(tri_pd, s));
     CU(c->b_mesh.upload(inst, s));           CU(c->b_mat.upload(mat, s));
 
     DevScene& sc = c->sc;
@@ -239,7 +249,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     sc.sph_shade = c->b_sph_shade.p; sc.sph_mat = c->b_sph_mat.p;
     sc.pla_normal = c->b_pla_normal.p; sc.pla_mat = c->b_pla_mat.p;
     sc.len_shade = c->b_len_shade.p; sc.len_mat = c->b_len_mat.p;
-    sc.tri_uv = c->b_tri_uv.p; sc.tri_mesh = c->b_tri_mesh.p;
+    sc.tri_uv = c->b_tri_uv.p; sc.tri_mesh = c->b_tri_mesh.p; sc.tri_pd = c->b_tri_pd.p;
     sc.mat = c->b_mat.p; sc.n_mat = d->n_materials;
     c->stats.n_primitives = d->n_spheres + d->n_planes + d->n_lenses + n_tri;
     c->stats.bvh_nodes = 0;
@@ -325,7 +335,7 @@ int rt_destroy(rt_ctx* c) {
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
         c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
-        c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_mesh.release();
+        c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_tri_pd.release(); c->b_mesh.release();
         if (c->ev0) cudaEventDestroy(c->ev0);
         if (c->ev1) cudaEventDestroy(c->ev1);
         if (c->own_stream) cudaStreamDestroy(c->own_stream);

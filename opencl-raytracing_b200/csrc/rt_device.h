@@ -42,6 +42,7 @@ struct DevScene {
     const uint32_t* len_mat;
     const float2* tri_uv;      // 3 per triangle (uvA, uvB, uvC)
     const uint32_t* tri_mesh;  // mesh instance of each triangle
+    const float* tri_pd;       // per triangle: plane offset n.A minus a safety margin (conservative front-side filter); padded to x4
     const float4* mat;         // 2 per material: (type as int bits, extra, -, -) (color.rgb, -)
     uint32_t n_mat;
 };

@@ -36,16 +36,23 @@ struct Hit {
     uint32_t aux;    // lens: side; triangle: index into the triangle stream
 };
 
-// Shared memory layout: [test stream | mesh table (3 x uint4 each) | per-warp front-face lists (1 KB / warp)]
+// Shared memory layout:
+//   [test stream | mesh table (3 x uint4 each) | triangle plane offsets (n_tri floats, padded to x4) | per-warp lists (1 KB / warp)]
+__device__ __forceinline__ uint32_t pd_f4(const DevScene& sc) { return (sc.n_tri + 3u) >> 2; }
 __device__ __forceinline__ void stage_scene(const DevScene& sc, float4* smem) {
-    const uint32_t n1 = sc.stream_f4, n2 = sc.n_mesh * 3u;
+    const uint32_t n1 = sc.stream_f4, n2 = sc.n_mesh * 3u, n3 = pd_f4(sc);
     const float4* m = reinterpret_cast<const float4*>(sc.mesh);
+    const float4* pd = reinterpret_cast<const float4*>(sc.tri_pd);
     for (uint32_t i = threadIdx.x; i < n1; i += blockDim.x) smem[i] = __ldg(sc.stream + i);
     for (uint32_t i = threadIdx.x; i < n2; i += blockDim.x) smem[n1 + i] = __ldg(m + i);
+    for (uint32_t i = threadIdx.x; i < n3; i += blockDim.x) smem[n1 + n2 + i] = __ldg(pd + i);
     __syncthreads();
 }
+__device__ __forceinline__ const float* smem_tri_pd(const DevScene& sc, const float4* smem) {
+    return reinterpret_cast<const float*>(smem + sc.stream_f4 + 3u * sc.n_mesh);
+}
 __device__ __forceinline__ uint8_t* warp_list(const DevScene& sc, float4* smem) {
-    return reinterpret_cast<uint8_t*>(smem + sc.stream_f4 + 3u * sc.n_mesh) + (threadIdx.x >> 5) * 1024u;
+    return reinterpret_cast<uint8_t*>(smem + sc.stream_f4 + 3u * sc.n_mesh + pd_f4(sc)) + (threadIdx.x >> 5) * 1024u;
 }
 
 // ---------------------------------------------------------------------------------- analytic primitives
@@ -185,8 +192,17 @@ __device__ __forceinline__ void hit_meshes_warp(const DevScene& sc, const float4
             const float4* T0 = S + sc.off_tri + 3u * (mi.x + c0);
             uint32_t cnt = 0u;
             if (open) {
-                for (uint32_t k = 0; k < chunk; ++k)
-                    if (front_facing<A>(T0 + 3u * k, d)) { list[cnt * 32u + lane] = (uint8_t)k; ++cnt; }
+                // A front-facing triangle can only be hit at t > 0 from the front side of its plane.  pdm is the
+                // plane offset n.A lowered by a safety margin on the host, o_margin covers the rounding of n.o, so
+                // this conservative filter only drops triangles whose Moller-Trumbore t would be negative.
+                const float* PD = smem_tri_pd(sc, S) + mi.x + c0;
+                const float o_margin = 4e-6f * (1.0f + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+                for (uint32_t k = 0; k < chunk; ++k) {
+                    const float4 q2 = T0[3u * k + 2u];
+                    const bool front = dot<A>(mk(q2.y, q2.z, q2.w), d) < 0.0f;                            // cl:285,295
+                    const bool ahead = fmaf(q2.y, o.x, fmaf(q2.z, o.y, fmaf(q2.w, o.z, o_margin))) >= PD[k];
+                    if (front && ahead) { list[cnt * 32u + lane] = (uint8_t)k; ++cnt; }
+                }
             }
             uint32_t incl = cnt;
 #pragma unroll
@@ -290,31 +306,37 @@ __device__ __forceinline__ uint32_t bounce_key(uint32_t hp, uint32_t sample, uin
 }
 __device__ __forceinline__ uint32_t draw(uint32_t hb, uint32_t j) { return mix32(hb + j * 0xC2B2AE35u); }
 __device__ __forceinline__ float u01(uint32_t h) { return (float)(h >> 8) * 5.9604644775390625e-8f; }
+__device__ __forceinline__ float u16f(uint32_t x) { return (float)x * 1.52587890625e-5f; }            // 16 bits -> [0,1)
 template <class A>
-__device__ __forceinline__ float s11(uint32_t h) { return A::sub(A::mul((float)(h >> 8), 1.1920928955078125e-7f), 1.0f); }
-// Uniform in the unit ball from exactly-rounded operations: Marsaglia disc rejection + max of 3 uniforms.
+__device__ __forceinline__ float s16f(uint32_t x) { return A::sub(A::mul((float)x, 3.0517578125e-5f), 1.0f); }   // -> [-1,1)
+// Uniform in the unit ball from exactly-rounded operations: Marsaglia disc rejection (one draw = two 16-bit
+// coordinates per try) + max of three 16-bit uniforms for the radius (CDF r^3, the law of cbrt(U)).
 template <class A>
-__device__ __forceinline__ V3 rng_ball(uint32_t hb, uint32_t base) {
+__device__ __forceinline__ V3 rng_ball(uint32_t hb, uint32_t base, uint32_t r3bits) {
     float u = 0.0f, v = 0.0f, s = 0.0f;
     for (uint32_t k = 0; k < 16u; ++k) {
-        u = s11<A>(draw(hb, base + 2u * k));
-        v = s11<A>(draw(hb, base + 2u * k + 1u));
+        const uint32_t h = draw(hb, base + k);
+        u = s16f<A>(h >> 16);
+        v = s16f<A>(h & 0xFFFFu);
         s = A::mad(v, v, A::mul(u, u));
         if (s < 1.0f) break;
         u = v = s = 0.0f;
     }
     const float q = A::sqrt(A::sub(1.0f, s));
     const float dx = A::mul(A::mul(2.0f, u), q), dy = A::mul(A::mul(2.0f, v), q), dz = A::sub(1.0f, A::mul(2.0f, s));
-    const float r = fmaxf(fmaxf(u01(draw(hb, base + 32u)), u01(draw(hb, base + 33u))), u01(draw(hb, base + 34u)));
+    const uint32_t hr = draw(hb, base + 16u);
+    const float r = fmaxf(fmaxf(u16f(hr >> 16), u16f(hr & 0xFFFFu)), u16f(r3bits));
     return mk(A::mul(dx, r), A::mul(dy, r), A::mul(dz, r));
 }
 // Same law as the reference's misaligned table read (cl:109-117): (a.x,a.y,a.z) | (a.y,a.z,b.x) | (a.z,b.x,b.y).
+// Draw 0: high half -> selector, low half -> third radius uniform of ball a.
 template <class A>
 __device__ __forceinline__ V3 counter_vec(uint32_t hb) {
-    const uint32_t sel = __umulhi(draw(hb, 0u), 3u);
-    const V3 a = rng_ball<A>(hb, 1u);
+    const uint32_t d0 = draw(hb, 0u);
+    const uint32_t sel = ((d0 >> 16) * 3u) >> 16;
+    const V3 a = rng_ball<A>(hb, 1u, d0 & 0xFFFFu);
     if (sel == 0u) return a;
-    const V3 b = rng_ball<A>(hb, 64u);
+    const V3 b = rng_ball<A>(hb, 33u, draw(hb, 50u) >> 16);
     return sel == 1u ? mk(a.y, a.z, b.x) : mk(a.z, b.x, b.y);
 }
 
@@ -577,7 +599,7 @@ __device__ __forceinline__ void probe_bounce_body(const ProbeLaunch& p, float4* 
 }
 
 inline size_t staged_bytes(const DevScene& sc) {
-    return ((size_t)sc.stream_f4 + 3u * sc.n_mesh) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
+    return ((size_t)sc.stream_f4 + 3u * sc.n_mesh + ((sc.n_tri + 3u) >> 2)) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
 }
 
 template <class K, class P>

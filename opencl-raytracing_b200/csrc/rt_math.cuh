@@ -44,7 +44,7 @@ struct Fused {
     static __device__ __forceinline__ float rcp(float a) { return __fdividef(1.0f, a); }
     static __device__ __forceinline__ float sqrt(float a) {
         float r;
-        asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
         return r;
     }
     static __device__ __forceinline__ float mad(float a, float b, float c) { return fmaf(a, b, c); }

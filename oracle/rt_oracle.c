@@ -291,30 +291,37 @@ uint32_t orc_rng_bounce_key(uint32_t seed, uint32_t pixel, uint32_t sample, uint
 }
 static inline uint32_t rng_draw(uint32_t hb, uint32_t j) { return orc_rng_mix32(hb + j * 0xC2B2AE35u); }
 static inline float u01(uint32_t h) { return (float)(h >> 8) * 5.9604644775390625e-8f; }          /* 2^-24 */
-static inline float s11(uint32_t h) { return (float)(h >> 8) * 1.1920928955078125e-7f - 1.0f; }   /* 2^-23 */
+static inline float u16f(uint32_t x) { return (float)x * 1.52587890625e-5f; }                    /* 16 bits -> [0,1)  */
+static inline float s16f(uint32_t x) { return (float)x * 3.0517578125e-5f - 1.0f; }              /* 16 bits -> [-1,1) */
 
 /* Uniform in the unit ball with exactly-rounded operations only: Marsaglia disc rejection for the
- * direction, max of three uniforms for the radius (CDF r^3, same law as cbrt(U), src/raytracer.cpp:79). */
-static v3 rng_ball(uint32_t hb, uint32_t base) {
+ * direction (one 32-bit draw = two 16-bit coordinates per try), max of three 16-bit uniforms for the
+ * radius (CDF r^3, same law as cbrt(U), src/raytracer.cpp:79).  r3 is supplied by the caller. */
+static v3 rng_ball(uint32_t hb, uint32_t base, uint32_t r3bits) {
     float u = 0.0f, v = 0.0f, s = 0.0f;
     for (uint32_t k = 0; k < 16; k++) {
-        u = s11(rng_draw(hb, base + 2 * k));
-        v = s11(rng_draw(hb, base + 2 * k + 1));
+        uint32_t h = rng_draw(hb, base + k);
+        u = s16f(h >> 16);
+        v = s16f(h & 0xFFFFu);
         s = u * u + v * v;
         if (s < 1.0f) break;
         u = v = s = 0.0f;
     }
     float q = sqrtf(1.0f - s);
     float dx = (2.0f * u) * q, dy = (2.0f * v) * q, dz = 1.0f - 2.0f * s;
-    float r = fmaxf(fmaxf(u01(rng_draw(hb, base + 32)), u01(rng_draw(hb, base + 33))), u01(rng_draw(hb, base + 34)));
+    uint32_t hr = rng_draw(hb, base + 16);
+    float r = fmaxf(fmaxf(u16f(hr >> 16), u16f(hr & 0xFFFFu)), u16f(r3bits));
     return V(dx * r, dy * r, dz * r);
 }
 /* The reference reads table floats [seed, seed+2] instead of [3 seed, 3 seed+2] (cl:109-117), so its
  * "random vector" is (a.x,a.y,a.z), (a.y,a.z,b.x) or (a.z,b.x,b.y) of two adjacent ball vectors with
- * probability 1/3 each.  The counter generator draws from that same law. */
+ * probability 1/3 each.  The counter generator draws from that same law.
+ * Draw 0: high half -> selector, low half -> third radius uniform of ball a. */
 void orc_rng_scatter_vec(uint32_t hb, float* out) {
-    uint32_t sel = (uint32_t)(((uint64_t)rng_draw(hb, 0) * 3u) >> 32);
-    v3 a = rng_ball(hb, 1), b = rng_ball(hb, 64);
+    uint32_t d0 = rng_draw(hb, 0);
+    uint32_t sel = ((d0 >> 16) * 3u) >> 16;
+    v3 a = rng_ball(hb, 1, d0 & 0xFFFFu);
+    v3 b = rng_ball(hb, 33, rng_draw(hb, 50) >> 16);
     v3 r = sel == 0 ? a : (sel == 1 ? V(a.y, a.z, b.x) : V(a.z, b.x, b.y));
     out[0] = r.x; out[1] = r.y; out[2] = r.z;
 }

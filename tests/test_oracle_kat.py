@@ -108,7 +108,7 @@ def test_counter_rng_known_answers(port, table):
     L = port.lib
     assert L.orc_rng_mix32(0) == 0 and L.orc_rng_mix32(1) == 0x688990C0 and L.orc_rng_mix32(0xDEADBEEF) == 0xE628C683
     assert L.orc_rng_bounce_key(9, 5, 3, 2) == 0x1BD6B6D1
-    assert np.allclose(port.scatter_vec(0x12345678), [0.14524782, 0.622163, -0.08723417], rtol=0, atol=1e-7)
+    assert np.allclose(port.scatter_vec(0x12345678), [-0.07291686534881592, -0.4501066207885742, -0.5408046245574951], rtol=0, atol=1e-7)
     assert L.orc_rng_uniform(0x12345678) == pytest.approx(0.9605576992034912, abs=1e-9)
     n = 40000
     v = np.array([port.scatter_vec(L.orc_rng_bounce_key(9, i, 0, 0)) for i in range(n)])
