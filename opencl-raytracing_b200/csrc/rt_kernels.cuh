@@ -72,6 +72,7 @@ __device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* _
             if (t >= RT_T_MIN && t < best.t) { best.t = t; best.id = (kKindSphere << 28) | i; }
         }
     }
+#pragma unroll 1
     for (uint32_t i = 0; i < sc.n_pla; ++i) {                       // cl:176-194
         const float4 p = S[sc.off_pla + 2 * i], n4 = S[sc.off_pla + 2 * i + 1];
         const V3 n = mk(n4.x, n4.y, n4.z);
@@ -80,6 +81,7 @@ __device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* _
         const float t = A::div(b, a);
         if (t >= RT_T_MIN && t < best.t) { best.t = t; best.id = (kKindPlane << 28) | i; }
     }
+#pragma unroll 1
     for (uint32_t i = 0; i < sc.n_len; ++i) {                       // cl:196-255
         const float4 l1 = S[sc.off_len + 2 * i], l2 = S[sc.off_len + 2 * i + 1];
         V3 oc = mk(A::sub(l1.x, o.x), A::sub(l1.y, o.y), A::sub(l1.z, o.z));
@@ -155,6 +157,13 @@ __device__ __forceinline__ void nearest_hit_lane(const DevScene& sc, const float
     best.t = RT_T_MAX; best.id = kIdMiss; best.bu = 0.0f; best.bv = 0.0f; best.aux = 0u;
     hit_analytic<A>(sc, S, o, d, best);
     hit_meshes_lane<A>(sc, S, o, d, mesh_mode, best);
+}
+// The Exact re-check of a knife-edge primary hit is cold code: keep it out of the hot instruction stream.
+static __device__ __noinline__ Hit nearest_hit_exact_cold(const DevScene& sc, const float4* __restrict__ S, float ox, float oy, float oz,
+                                                          float dx, float dy, float dz, uint32_t mesh_mode) {
+    Hit best;
+    nearest_hit_lane<Exact>(sc, S, mk(ox, oy, oz), mk(dx, dy, dz), mesh_mode, best);
+    return best;
 }
 
 // ---------------------------------------------------------------------------------- warp-cooperative meshes
@@ -519,7 +528,7 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
         nearest_hit_warp<A>(p.sc, S, list, o, d, active, p.mesh_mode, h);
         if (active) {
             if (!A::kExact && p.certify_id && i == 0u && h.id != certified)
-                nearest_hit_lane<Exact>(p.sc, S, o, d, p.mesh_mode, h);     // knife-edge pixel: take the exact primary hit
+                h = nearest_hit_exact_cold(p.sc, S, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);   // knife-edge pixel: take the exact primary hit
             ++rays;
             bool ended;
             if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }   // cl:450-452
@@ -566,7 +575,7 @@ __device__ __forceinline__ void probe_hits_body(const ProbeLaunch& p, float4* sm
     Hit h;
     nearest_hit_warp<A>(p.sc, smem, list, o, d, active, p.mesh_mode, h);
     if (!active) return;
-    if (!A::kExact && p.certify_id && h.id != p.certify_id[i]) nearest_hit_lane<Exact>(p.sc, smem, o, d, p.mesh_mode, h);
+    if (!A::kExact && p.certify_id && h.id != p.certify_id[i]) h = nearest_hit_exact_cold(p.sc, smem, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);
     if (p.out_id) p.out_id[i] = h.id;
     if (p.out_t) p.out_t[i] = h.t;
 }

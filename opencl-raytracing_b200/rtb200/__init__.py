@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "librtb200.so")
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "librtb200.so")
 
 RNG_TABLE, RNG_COUNTER = 0, 1
 ARITH_STRICT, ARITH_FAST = 0, 1
