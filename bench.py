@@ -172,9 +172,9 @@ def main_b200(a):
     accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
     ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+    from rtb200.multigpu import reduce_to_rank0, sample_range
     spp = a.spp
-    first = rank * spp // world
-    n_mine = (rank + 1) * spp // world - first
+    first, n_mine = sample_range(spp, world, rank)
 
     peak_gslots, nominal_mhz = rtb200.measure_fp32_peak(local)
 
@@ -183,8 +183,7 @@ def main_b200(a):
         ctx.render_samples(cam, first, n_mine, rtb200.ACCUM_SUM)
         rays = ctx.stats().rays_last
         kms = ctx.stats().ms_last
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_to_rank0(accum)
         if rank == 0:
             ctx.finalize(spp)
         return rays, kms
