@@ -126,6 +126,22 @@ int rt_trace_rays(rt_ctx* ctx, const float* rays6, uint32_t n, uint32_t* out_id,
 int rt_bounce_rays(rt_ctx* ctx, float* rays6, uint32_t n, const uint32_t* sample, const uint32_t* bounce,
                    const uint32_t* gx, const uint32_t* gy, float* col3, uint8_t* ended);
 
+/* ---- host-only helpers: the C view of the C++ host classes (no CUDA device needed) -------------------------
+ * SceneCreator::loadScene + loadTextures (src/scene.cpp:145-190, 297-403): parse a .scene file in the reference's
+ * grammar, import its OBJ models and PNG textures.  asset_root replaces the working directory the reference
+ * resolves paths against; texture_dir (may be NULL) is where .mtl texture basenames are looked up. */
+typedef struct rt_scene rt_scene;
+int rt_scene_load(const char* scene_path, const char* asset_root, const char* texture_dir, rt_scene** out);
+int rt_scene_get_desc(const rt_scene* scene, rt_scene_desc* out);
+int rt_scene_get_textures(const rt_scene* scene, const float** rgba, int* width, int* height, int* layers);
+int rt_scene_upload(const rt_scene* scene, rt_ctx* ctx);       /* SceneCreator::createScene */
+int rt_scene_free(rt_scene* scene);
+/* Camera(fov, aspect, pos, yaw, pitch).transferData() (src/camera.cpp:46-51, 94-118). */
+int rt_camera_data(int fov_degrees, float aspect, const float pos[3], float yaw, float pitch, float out[12]);
+/* Uncompressed 24-bit TGA of the (sqrt(mean),1) image, layout of main.cpp:262-289 (18-byte header, BGR, bottom-up),
+ * values clamped to [0,1].  The reference reads the GL front buffer; here the float image is converted. */
+int rt_write_tga(const char* path, const float* rgba, int width, int height);
+
 /* Measured FP32 issue peak of the device (dependent-free FFMA loop on every SM): G lane-instructions/s. */
 int rt_measure_fp32_peak(int device, double* gslots_per_s, double* sm_clock_mhz);
 

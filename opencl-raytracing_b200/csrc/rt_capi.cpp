@@ -285,6 +285,7 @@ int ensure_certified(rt_ctx* c, const float* cam) {
 extern "C" {
 
 const char* rt_last_error(void) { return g_last_error.c_str(); }
+int rt_set_error_message(int code, const char* msg) { return fail(code, "%s", msg ? msg : ""); }   // used by host/host_capi.cpp
 const char* rt_version(void) { return "rtb200 0.1 (sm_100a; strict+fast arithmetic; table+counter RNG)"; }
 
 int rt_create(int width, int height, int device, rt_ctx** out) {

@@ -75,6 +75,10 @@ def lib():
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
         "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
         "rt_measure_fp32_peak": [ci, C.POINTER(C.c_double), C.POINTER(C.c_double)],
+        "rt_scene_load": [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)], "rt_scene_get_desc": [vp, C.POINTER(SceneDesc)],
+        "rt_scene_get_textures": [vp, C.POINTER(vp), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)],
+        "rt_scene_upload": [vp, vp], "rt_scene_free": [vp],
+        "rt_camera_data": [ci, C.c_float, vp, C.c_float, C.c_float, vp], "rt_write_tga": [C.c_char_p, vp, ci, ci],
     }
     for name, args in sig.items():
         f = getattr(L, name)
@@ -112,6 +116,47 @@ def measure_fp32_peak(device=0):
     g, mhz = C.c_double(0), C.c_double(0)
     _check(lib().rt_measure_fp32_peak(device, C.byref(g), C.byref(mhz)))
     return g.value, mhz.value
+
+
+ITEM_BYTES = dict(materials=48, spheres=32, planes=48, lenses=64, vertices=16, uvs=8, indices=4, meshes=16, models=12)
+
+
+def load_scene_file(scene_path, asset_root="", texture_dir=None):
+    """SceneCreator::loadScene + loadTextures through the C++ host classes (no GPU needed).
+    -> (arrays dict of (n, itemsize) uint8 copies in the reference's host layouts, float textures [L,H,W,4] or None)."""
+    L = lib()
+    h = C.c_void_p()
+    _check(L.rt_scene_load(scene_path.encode(), (asset_root or "").encode(), texture_dir.encode() if texture_dir else None, C.byref(h)))
+    try:
+        d = SceneDesc()
+        _check(L.rt_scene_get_desc(h, C.byref(d)))
+        arrays = {}
+        for name, nb in ITEM_BYTES.items():
+            n = getattr(d, "n_" + name)
+            ptr = getattr(d, name)
+            arrays[name] = (np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n * nb,)).reshape(n, nb).copy()
+                            if n else np.zeros((0, nb), np.uint8))
+        p, w, hh, layers = C.c_void_p(), ci_(), ci_(), ci_()
+        _check(L.rt_scene_get_textures(h, C.byref(p), C.byref(w), C.byref(hh), C.byref(layers)))
+        tex = None
+        if layers.value > 0:
+            n = layers.value * hh.value * w.value * 4
+            tex = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(n,)).reshape(layers.value, hh.value, w.value, 4).copy()
+        return arrays, tex
+    finally:
+        L.rt_scene_free(h)
+
+
+def ci_():
+    return C.c_int(0)
+
+
+def camera_data(fov, aspect, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):
+    """Camera(fov, aspect, pos, yaw, pitch).transferData() of the C++ host class."""
+    out = np.zeros(12, np.float32)
+    p = np.asarray(pos, np.float32)
+    _check(lib().rt_camera_data(int(fov), float(aspect), p.ctypes.data, float(yaw), float(pitch), out.ctypes.data))
+    return out
 
 
 class Context:

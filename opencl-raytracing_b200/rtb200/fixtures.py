@@ -30,8 +30,13 @@ def load_scene_npz(path):
 
 def textures_to_float(rgba8):
     """8-bit RGBA -> float RGBA the way stbi_loadf does: pow(c/255, 2.2) on RGB, a/255 on alpha."""
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+    libm.powf.restype = ctypes.c_float
+    libm.powf.argtypes = [ctypes.c_float, ctypes.c_float]
     c = (np.arange(256, dtype=np.float32) / np.float32(255.0)).astype(np.float32)
-    rgb = np.power(c.astype(np.float64), np.float64(np.float32(2.2))).astype(np.float32)
+    rgb = np.array([libm.powf(float(x), 2.2) for x in c], dtype=np.float32)
     out = np.empty(rgba8.shape, dtype=np.float32)
     out[..., :3] = rgb[rgba8[..., :3]]
     out[..., 3] = c[rgba8[..., 3]]

@@ -49,6 +49,8 @@ _libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
 for _n in ("cosf", "sinf", "tanf", "sqrtf"):
     getattr(_libm, _n).restype = ctypes.c_float
     getattr(_libm, _n).argtypes = [ctypes.c_float]
+_libm.powf.restype = ctypes.c_float
+_libm.powf.argtypes = [ctypes.c_float, ctypes.c_float]
 
 
 def _cosf(x): return f32(_libm.cosf(float(x)))
@@ -205,11 +207,12 @@ _STB_LUT = None
 
 
 def stb_ldr_to_hdr_lut():
-    """stb_image stbi__ldr_to_hdr: (float)(pow(c / 255.0f, 2.2f) * 1.0f); alpha: c / 255.0f."""
+    """stb_image stbi__ldr_to_hdr: (float)(pow(c / 255.0f, 2.2f) * 1.0f); alpha: c / 255.0f.  stb_image.h is compiled
+    inside a C++ translation unit in the reference (src/scene.cpp:16-17), where pow(float, float) is powf."""
     global _STB_LUT
     if _STB_LUT is None:
         c = (np.arange(256, dtype=f32) / f32(255.0)).astype(f32)
-        rgb = np.power(c.astype(np.float64), np.float64(f32(2.2))).astype(f32)
+        rgb = np.array([_libm.powf(float(x), 2.2) for x in c], dtype=f32)
         _STB_LUT = (rgb, c)
     return _STB_LUT
 

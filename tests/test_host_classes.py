@@ -1,0 +1,106 @@
+"""CPU tests of the C++ host classes (SceneCreator, Camera — include/scene.h, include/camera.h) through their C view
+(rt_scene_load, rt_camera_data): compared bit for bit with the oracle's numpy restatement of the reference's host
+code (oracle/scene_py.py) on repository-owned assets, plus the reference's error messages (src/scene.cpp)."""
+import os
+
+import numpy as np
+import pytest
+
+import scene_py as sp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ASSETS = os.path.join(ROOT, "tests", "golden", "assets")
+FIELDS = {"materials": (sp.MATERIAL_DT, ["type", "color", "extra"]), "spheres": (sp.SPHERE_DT, ["pos", "r", "mat"]),
+          "planes": (sp.PLANE_DT, ["pos", "normal", "mat"]), "lenses": (sp.LENS_DT, ["pos", "p1", "p2", "r1", "r2", "mat"])}
+
+
+def assert_same_scene(got, want):
+    for name, (dt, fields) in FIELDS.items():
+        g = got[name].reshape(-1).view(dt)
+        w = want[name]
+        assert g.shape == w.shape, name
+        for f in fields:
+            a, b = np.ascontiguousarray(g[f]), np.ascontiguousarray(w[f])
+            if a.dtype.kind == "f":
+                a, b = a.reshape(len(g), -1)[:, :3 if a.ndim > 1 else None], b.reshape(len(w), -1)[:, :3 if b.ndim > 1 else None]
+                assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), (name, f)
+            else:
+                assert np.array_equal(a, b), (name, f)
+    assert np.array_equal(got["vertices"].view(np.float32)[:, :3].view(np.uint32), want["vertices"][:, :3].view(np.uint32))
+    assert np.array_equal(got["uvs"].view(np.float32).view(np.uint32), np.ascontiguousarray(want["uvs"]).view(np.uint32))
+    assert np.array_equal(got["indices"].view(np.uint32).ravel(), want["indices"])
+    assert np.array_equal(got["meshes"].view(np.uint32), np.ascontiguousarray(want["meshes"]).view(np.uint32).reshape(-1, 4))
+    assert np.array_equal(got["models"].view(np.uint32), np.ascontiguousarray(want["models"]).view(np.uint32).reshape(-1, 3))
+
+
+def test_own_scene_matches_python_restatement():
+    import rtb200
+    arr, tex = rtb200.load_scene_file("shapes.scene", ASSETS, ASSETS)
+    sc = sp.parse_scene_file(os.path.join(ASSETS, "shapes.scene"), root=ASSETS)
+    sc.load_textures(lambda p: os.path.join(ASSETS, os.path.basename(p)))
+    want = sc.arrays()
+    assert_same_scene(arr, want)
+    assert [len(arr[k]) for k in ("materials", "spheres", "planes", "lenses", "models", "meshes")] == [6, 4, 1, 1, 1, 2]
+    assert len(arr["vertices"]) == 4 * 3 + 3 * 2 + 4 and len(arr["indices"]) == 3 * (2 * 3 + 2 + 2)   # corners unrolled, quads fanned
+    assert tex.shape == (2, 32, 32, 4)
+    assert np.array_equal(tex.view(np.uint32), sp.texture_from_rgba8(want["textures_rgba8"]).view(np.uint32))
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/assets/scenes/scene.scene"), reason="reference tree not present")
+def test_reference_default_scene_matches_python_restatement_and_fixture(scenes):
+    import rtb200
+    arr, tex = rtb200.load_scene_file("assets/scenes/scene.scene", "/root/reference")
+    sc = sp.parse_scene_file("/root/reference/assets/scenes/scene.scene", root="/root/reference")
+    sc.load_textures(lambda p: "/root/reference/assets/textures/" + os.path.basename(p))
+    assert_same_scene(arr, sc.arrays())
+    assert [len(arr[k]) for k in ("materials", "spheres", "planes", "lenses", "models", "meshes")] == [9, 8, 1, 1, 2, 2]
+    assert len(arr["vertices"]) == 48 and len(arr["indices"]) == 72
+    assert np.array_equal(tex.view(np.uint32), scenes["default"][1].view(np.uint32))   # the committed fixture
+
+
+@pytest.mark.parametrize("name,message", [
+    ("bad_material.scene", "ERROR: SCENE: MATERIAL: shiny DOES NOT EXIST"),
+    ("bad_vector.scene", "ERROR: SCENE: IMPROPER VECTOR: (0 , 0, 3)"),
+    ("bad_uint.scene", "ERROR: SCENE: IMPROPER UNSIGNED INT:  10"),
+    ("bad_float.scene", "ERROR: SCENE: IMPROPER FLOAT:  1e3"),
+    ("missing_param.scene", "ERROR: SCENE: NOT ENOUGH PARAMETERS"),
+    ("no_section.scene", "ERROR: SCENE: OPERATION NOT SPECIFIED"),
+    ("bad_operation.scene", "ERROR: SCENE: OPERATION rotate DOES NOT EXIST"),
+    ("blank_line.scene", "ERROR: SCENE: MATERIAL:     DOES NOT EXIST"),
+    ("bad_path.scene", "ERROR: SCENE: IMPROPER PATH:  shapes.obj"),
+    ("no_material.scene", "ERROR: MATERIAL OF ID: 3 DOES NOT EXIST"),
+    ("untextured_model.scene", "ERROR: TEXTURE COUNT = 0"),
+    ("does_not_exist.scene", "ERROR: SCENE: NOT SUCCESFULLY READ"),
+])
+def test_error_messages_of_the_reference(name, message):
+    import rtb200
+    with pytest.raises(rtb200.RtError) as e:
+        rtb200.load_scene_file(name, ASSETS, ASSETS)
+    assert message in str(e.value)
+    if name != "does_not_exist.scene":
+        with pytest.raises(sp.SceneError) as e2:
+            s = sp.parse_scene_file(os.path.join(ASSETS, name), root=ASSETS)
+            s.load_textures(lambda p: os.path.join(ASSETS, os.path.basename(p)))
+        assert message in str(e2.value)
+
+
+def test_camera_matches_python_restatement():
+    import rtb200
+    for args in ((60, 800 / 600), (60, 1920 / 1080, (0, 0, 0), 0, 0), (45, 1.5, (1, -2, 3), 30.0, -10.0), (90, 1.0, (0, 0, 0), 359.0, 89.0)):
+        assert np.array_equal(rtb200.camera_data(*args).view(np.uint32), sp.camera_data(*args).view(np.uint32))
+    c = rtb200.camera_data(60, 4 / 3)
+    assert np.allclose(c[3:6] + 0.5 * c[6:9] + 0.5 * c[9:12], [0, 0, 1], atol=1e-6)      # centre of the view looks down +z
+    assert c[10] < 0                                                                        # screen-up is world -y
+
+
+def test_tga_layout(tmp_path):
+    import rtb200
+    img = np.zeros((2, 3, 4), np.float32)
+    img[0, 0, :3] = (1.0, 0.5, 0.0)
+    img[1, 2, :3] = (0.0, 0.0, 2.0)    # clamped
+    p = str(tmp_path / "t.tga")
+    assert rtb200.lib().rt_write_tga(p.encode(), img.ctypes.data, 3, 2) == 0
+    b = open(p, "rb").read()
+    assert len(b) == 18 + 3 * 2 * 3
+    assert np.frombuffer(b[:18], np.uint16).tolist() == [0, 2, 0, 0, 0, 0, 3, 2, 24]
+    assert list(b[18:21]) == [0, 128, 255] and list(b[18 + 15:18 + 18]) == [255, 0, 0]    # BGR, bottom row first
