@@ -1,0 +1,44 @@
+// csrc/rt_bvh.h — GPU-built LBVH over the finite primitives of a scene (spheres, lenses, triangles).
+// The reference is brute force only (kernels/raytracer.cl:322-360, O(N) per ray); north_star asks for a GPU-built
+// LBVH "that must return the same nearest hit as brute force".  Planes are unbounded and stay in the brute list.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace rtb {
+
+// Traversal node: both children's boxes live in the parent, so one 64-byte fetch decides two subtrees.
+// child >= 0: internal node index; child < 0: leaf, slot = ~child.
+struct alignas(16) BvhNode {
+    float lo0[3]; int32_t child0;
+    float hi0[3]; int32_t child1;
+    float lo1[3]; uint32_t pad0;
+    float hi1[3]; uint32_t pad1;
+};
+static_assert(sizeof(BvhNode) == 64, "one node = four 16-byte words");
+
+struct DevBvh {
+    const BvhNode* nodes;     // n_leaves - 1 internal nodes, root = 0 (n_leaves >= 2)
+    const uint2* leaves;      // per leaf slot: (hit id = kind << 28 | reference index, stream index of the primitive)
+    uint32_t n_leaves;        // 0 = no BVH (brute-force path)
+    int32_t root;             // 0, or ~0 when the tree is a single leaf
+};
+
+struct BvhBuildInput {        // device pointers into the scene buffers
+    const float4* stream;     // test stream (see rt_device.h)
+    uint32_t off_len, off_tri;
+    uint32_t n_sph, n_len, n_tri;
+    const uint32_t* tri_face_id;   // reference-global face number per stream triangle
+};
+
+struct BvhBuffers {           // owned by the context; (re)allocated by build_lbvh
+    BvhNode* nodes = nullptr;
+    uint2* leaves = nullptr;
+    uint32_t n_leaves = 0;
+};
+
+// Morton codes -> radix sort (CUB) -> Karras hierarchy -> bottom-up refit -> traversal nodes; all on `stream`.
+cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t stream);
+void free_lbvh(BvhBuffers& b);
+
+}  // namespace rtb

@@ -5,6 +5,7 @@
 // RayTracer::createCLBuffers/setKernelArgs/render/renderAgain (src/raytracer.cpp:63-165) and of
 // SceneCreator::setupBuffers/createScene (src/scene.cpp:46-87) in the reference.
 #include "../../include/rt_capi.h"
+#include "rt_bvh.h"
 #include "rt_device.h"
 
 #include <algorithm>
@@ -83,8 +84,10 @@ struct rt_ctx {
     DevBuf<float4> b_stream, b_sph_shade, b_pla_normal, b_len_shade, b_mat;
     DevBuf<uint32_t> b_sph_mat, b_pla_mat, b_len_mat, b_tri_mesh;
     DevBuf<float2> b_tri_uv;
-    DevBuf<float> b_tri_pd;
-    DevBuf<MeshInst> b_mesh;
+    DevBuf<uint32_t> b_tri_face;      // reference-global face number per stream triangle (BVH leaf ids)
+    BvhBuffers bvh;                   // GPU-built LBVH (empty while the brute-force path is active)
+    size_t staged_bytes = 0;          // shared memory the brute-force path needs for this scene
+    uint32_t n_finite = 0;            // spheres + lenses + triangles
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
     uint32_t sample_counter = 0;
     int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
@@ -136,6 +139,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     std::vector<uint32_t> sph_mat, pla_mat, len_mat, tri_mesh;
     std::vector<float2> tri_uv;
     std::vector<float> tri_pd;
+    std::vector<uint32_t> tri_face;
     std::vector<MeshInst> inst;
 
     for (uint32_t i = 0; i < d->n_spheres; ++i) {
@@ -207,6 +211,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
                 }
                 tri_uv.push_back(uv[0]); tri_uv.push_back(uv[1]); tri_uv.push_back(uv[2]);
                 tri_mesh.push_back((uint32_t)inst.size());
+                tri_face.push_back(mi.face_id_base + f);
                 ++n_tri;
             }
             if (!corners.empty()) {
@@ -229,34 +234,77 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
     }
     while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
-    const size_t staged = (stream.size() + 3 * inst.size() + tri_pd.size() / 4) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
-    if (staged > kMaxStagedBytes)
-        return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); BVH path required", staged, kMaxStagedBytes);
+    while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
+    c->staged_bytes = (stream.size() + 3 * inst.size() + tri_pd.size() / 4) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
+    c->n_finite = d->n_spheres + d->n_lenses + n_tri;
+    if (c->prm.accel == RT_ACCEL_BRUTE && c->staged_bytes > kMaxStagedBytes)
+        return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); use RT_ACCEL_AUTO or RT_ACCEL_BVH",
+                    c->staged_bytes, kMaxStagedBytes);
+
+    // one contiguous device buffer with the layout the kernels stage into shared memory:
+    // [test stream | mesh-instance table (3 x 16 B each) | plane offsets (padded to x4)]
+    const size_t stream_f4 = stream.size();
+    std::vector<float4> all(stream);
+    all.resize(stream_f4 + 3 * inst.size() + tri_pd.size() / 4);
+    if (!inst.empty()) std::memcpy(all.data() + stream_f4, inst.data(), inst.size() * sizeof(MeshInst));
+    if (!tri_pd.empty()) std::memcpy(all.data() + stream_f4 + 3 * inst.size(), tri_pd.data(), tri_pd.size() * sizeof(float));
 
     cudaStream_t s = c->stream;
-    CU(c->b_stream.upload(stream, s));       CU(c->b_sph_shade.upload(sph_shade, s)); CU(c->b_sph_mat.upload(sph_mat, s));
+    CU(c->b_stream.upload(all, s));          CU(c->b_sph_shade.upload(sph_shade, s)); CU(c->b_sph_mat.upload(sph_mat, s));
     CU(c->b_pla_normal.upload(pla_normal, s)); CU(c->b_pla_mat.upload(pla_mat, s));
     CU(c->b_len_shade.upload(len_shade, s)); CU(c->b_len_mat.upload(len_mat, s));
     CU(c->b_tri_uv.upload(tri_uv, s));       CU(c->b_tri_mesh.upload(tri_mesh, s));
-    CU(c->b_tri_pd.upload(tri_pd, s));
-    CU(c->b_mesh.upload(inst, s));           CU(c->b_mat.upload(mat, s));
+    CU(c->b_tri_face.upload(tri_face, s));   CU(c->b_mat.upload(mat, s));
 
     DevScene& sc = c->sc;
-    sc.stream = c->b_stream.p; sc.stream_f4 = (uint32_t)stream.size();
+    sc.stream = c->b_stream.p; sc.stream_f4 = (uint32_t)stream_f4;
     sc.n_sph = d->n_spheres; sc.n_pla = d->n_planes; sc.n_len = d->n_lenses; sc.n_tri = n_tri; sc.n_mesh = (uint32_t)inst.size();
     sc.off_pla = off_pla; sc.off_len = off_len; sc.off_tri = off_tri;
-    sc.mesh = c->b_mesh.p;
+    sc.mesh = reinterpret_cast<const MeshInst*>(c->b_stream.p + stream_f4);
     sc.sph_shade = c->b_sph_shade.p; sc.sph_mat = c->b_sph_mat.p;
     sc.pla_normal = c->b_pla_normal.p; sc.pla_mat = c->b_pla_mat.p;
     sc.len_shade = c->b_len_shade.p; sc.len_mat = c->b_len_mat.p;
-    sc.tri_uv = c->b_tri_uv.p; sc.tri_mesh = c->b_tri_mesh.p; sc.tri_pd = c->b_tri_pd.p;
+    sc.tri_uv = c->b_tri_uv.p; sc.tri_mesh = c->b_tri_mesh.p; sc.tri_pd = reinterpret_cast<const float*>(c->b_stream.p + stream_f4 + 3 * inst.size());
     sc.mat = c->b_mat.p; sc.n_mat = d->n_materials;
     c->stats.n_primitives = d->n_spheres + d->n_planes + d->n_lenses + n_tri;
     c->stats.bvh_nodes = 0;
+    free_lbvh(c->bvh);
     c->max_texture_used = max_tex;
     c->certify_valid = false;
     c->have_scene = true;
     return RT_OK;
+}
+
+// Pick the intersection path for the current scene and parameters and build the LBVH on demand.
+// RT_ACCEL_AUTO: brute force from shared memory while the scene fits and has at most 512 finite primitives.
+int ensure_accel(rt_ctx* c) {
+    bool want_bvh = c->prm.accel == RT_ACCEL_BVH;
+    if (c->prm.accel == RT_ACCEL_AUTO) want_bvh = c->staged_bytes > kMaxStagedBytes || c->n_finite > 512u;
+    if (c->prm.accel == RT_ACCEL_BRUTE && c->staged_bytes > kMaxStagedBytes)
+        return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu)", c->staged_bytes, kMaxStagedBytes);
+    if (want_bvh && c->n_finite == 0) want_bvh = false;
+    if (!want_bvh) {
+        if (c->bvh.n_leaves) { free_lbvh(c->bvh); c->stats.bvh_nodes = 0; c->certify_valid = false; }
+        return RT_OK;
+    }
+    if (c->sc.n_tri > 0 && c->prm.mesh_mode != RT_MESH_NEAREST)
+        return fail(RT_ERR_UNSUPPORTED, "the LBVH path answers the nearest-front-facing mesh rule only: set mesh_mode = RT_MESH_NEAREST "
+                                        "(the reference's first-front-facing-in-face-order rule depends on scan order)");
+    if (c->bvh.n_leaves == c->n_finite) return RT_OK;
+    BvhBuildInput in{};
+    in.stream = c->sc.stream; in.off_len = c->sc.off_len; in.off_tri = c->sc.off_tri;
+    in.n_sph = c->sc.n_sph; in.n_len = c->sc.n_len; in.n_tri = c->sc.n_tri; in.tri_face_id = c->b_tri_face.p;
+    CU(build_lbvh(in, c->bvh, c->stream));
+    c->stats.bvh_nodes = c->bvh.n_leaves > 1 ? c->bvh.n_leaves - 1 : 1;
+    c->stats.kernel_launches += 8;
+    c->certify_valid = false;
+    return RT_OK;
+}
+DevBvh dev_bvh(const rt_ctx* c) {
+    DevBvh b{};
+    b.nodes = c->bvh.nodes; b.leaves = c->bvh.leaves; b.n_leaves = c->bvh.n_leaves;
+    b.root = c->bvh.n_leaves > 1 ? 0 : ~0;
+    return b;
 }
 
 // Fast arithmetic certifies its primary hits: one Exact nearest-hit query per pixel, recomputed only when the
@@ -270,7 +318,7 @@ int ensure_certified(rt_ctx* c, const float* cam) {
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     std::memcpy(L.cam, cam, 48);
     L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth; L.mesh_mode = c->prm.mesh_mode;
-    L.n = (uint32_t)n; L.out_id = c->d_certify;
+    L.n = (uint32_t)n; L.out_id = c->d_certify; L.bvh = dev_bvh(c);
     CU(launch_probe_hits_strict(L, c->stream));
     c->stats.kernel_launches += 1;
     std::memcpy(c->certify_cam, cam, 48);
@@ -336,7 +384,7 @@ int rt_destroy(rt_ctx* c) {
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
         c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
-        c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_tri_pd.release(); c->b_mesh.release();
+        c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_tri_face.release(); free_lbvh(c->bvh);
         if (c->ev0) cudaEventDestroy(c->ev0);
         if (c->ev1) cudaEventDestroy(c->ev1);
         if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -424,7 +472,9 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
                     (long long)c->max_texture_used, c->tex.layers);
     if (n == 0) return RT_OK;
     Guard g(c);
+    { int r = ensure_accel(c); if (r != RT_OK) return r; }
     TraceLaunch L{};
+    L.bvh = dev_bvh(c);
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     std::memcpy(L.cam, cam, 12 * sizeof(float));
     L.W = c->W; L.H = c->H; L.first = first; L.n = n; L.depth = c->prm.max_depth;
@@ -551,6 +601,7 @@ ProbeLaunch base_probe(const rt_ctx* c) {
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth;
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.mesh_mode = c->prm.mesh_mode;
+    L.bvh = dev_bvh(c);
     return L;
 }
 }  // namespace
@@ -562,6 +613,7 @@ int rt_read_primary_ids(rt_ctx* c, const float cam[12], uint32_t* ids, float* t)
     Guard g(c);
     const size_t n = (size_t)c->W * c->H;
     Scratch s;
+    { int r_ = ensure_accel(c); if (r_ != RT_OK) return r_; }
     ProbeLaunch L = base_probe(c);
     std::memcpy(L.cam, cam, 12 * sizeof(float));
     L.n = (uint32_t)n;
@@ -586,6 +638,7 @@ int rt_trace_rays(rt_ctx* c, const float* rays6, uint32_t n, uint32_t* out_id, f
     if (n == 0) return RT_OK;
     Guard g(c);
     Scratch s;
+    { int r_ = ensure_accel(c); if (r_ != RT_OK) return r_; }
     ProbeLaunch L = base_probe(c);
     float* d_rays6 = nullptr;
     CU(s.alloc(&d_rays6, (size_t)n * 6));
@@ -609,6 +662,7 @@ int rt_bounce_rays(rt_ctx* c, float* rays6, uint32_t n, const uint32_t* sample, 
     if (n == 0) return RT_OK;
     Guard g(c);
     Scratch s;
+    { int r_ = ensure_accel(c); if (r_ != RT_OK) return r_; }
     ProbeLaunch L = base_probe(c);
     float *d_in = nullptr, *d_out = nullptr, *d_col = nullptr;
     uint32_t *d_s = nullptr, *d_b = nullptr, *d_x = nullptr, *d_y = nullptr;

@@ -8,6 +8,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "rt_bvh.h"
+
 namespace rtb {
 
 // ---- test stream (float4 units), in hitScene order: spheres, planes, lenses, then mesh instances -------------
@@ -64,6 +66,7 @@ struct TraceLaunch {
     float4* target;            // image (reference chain) or accumulation buffer (sum)
     unsigned long long* rays;  // device counter
     const uint32_t* certify_id; // fast arithmetic: Exact primary-hit id per pixel (nullptr = no certification)
+    DevBvh bvh;                // n_leaves == 0: brute-force path over the staged scene
 };
 
 struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays
@@ -82,6 +85,7 @@ struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounc
     float* col3;
     uint8_t* ended;
     const uint32_t* certify_id; // fast arithmetic: Exact hit id per ray (nullptr = no certification)
+    DevBvh bvh;
 };
 
 static_assert(sizeof(MeshInst) == 48, "MeshInst is three 16-byte words");

@@ -16,6 +16,7 @@
 //     reordering does not change any result;
 //   * hit-point data (position, normal, uv, material) is derived once, for the winning primitive only.
 #pragma once
+#include "rt_bvh.h"
 #include "rt_device.h"
 #include "rt_math.cuh"
 
@@ -40,12 +41,9 @@ struct Hit {
 //   [test stream | mesh table (3 x uint4 each) | triangle plane offsets (n_tri floats, padded to x4) | per-warp lists (1 KB / warp)]
 __device__ __forceinline__ uint32_t pd_f4(const DevScene& sc) { return (sc.n_tri + 3u) >> 2; }
 __device__ __forceinline__ void stage_scene(const DevScene& sc, float4* smem) {
-    const uint32_t n1 = sc.stream_f4, n2 = sc.n_mesh * 3u, n3 = pd_f4(sc);
-    const float4* m = reinterpret_cast<const float4*>(sc.mesh);
-    const float4* pd = reinterpret_cast<const float4*>(sc.tri_pd);
-    for (uint32_t i = threadIdx.x; i < n1; i += blockDim.x) smem[i] = __ldg(sc.stream + i);
-    for (uint32_t i = threadIdx.x; i < n2; i += blockDim.x) smem[n1 + i] = __ldg(m + i);
-    for (uint32_t i = threadIdx.x; i < n3; i += blockDim.x) smem[n1 + n2 + i] = __ldg(pd + i);
+    // the global buffer has the same layout as the shared-memory copy: [stream | mesh table | plane offsets]
+    const uint32_t n = sc.stream_f4 + sc.n_mesh * 3u + pd_f4(sc);
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) smem[i] = __ldg(sc.stream + i);
     __syncthreads();
 }
 __device__ __forceinline__ const float* smem_tri_pd(const DevScene& sc, const float4* smem) {
@@ -57,21 +55,44 @@ __device__ __forceinline__ uint8_t* warp_list(const DevScene& sc, float4* smem) 
 
 // ---------------------------------------------------------------------------------- analytic primitives
 // cl:149-255 (spheres, planes, lenses) in hitScene order (cl:327-349); strict `<` keeps the earlier one on ties.
+// cl:149-174: near root if it is in range, else the far root; the caller applies t >= T_MIN and the best-so-far test.
 template <class A>
-__device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* __restrict__ S, V3 o, V3 d, Hit& best) {
-    for (uint32_t i = 0; i < sc.n_sph; ++i) {                       // cl:149-174
-        const float4 s = S[i];
-        const V3 oc = mk(A::sub(s.x, o.x), A::sub(s.y, o.y), A::sub(s.z, o.z));
-        const float b = dot<A>(oc, d);
-        const float c = A::sub(dot<A>(oc, oc), s.w);
-        const float dis = A::msub(b, b, c);
-        if (dis > 0.0f) {
-            const float sq = A::sqrt(dis);
-            float t = A::sub(b, sq);
-            if (!in_range(t)) t = A::add(b, sq);
-            if (t >= RT_T_MIN && t < best.t) { best.t = t; best.id = (kKindSphere << 28) | i; }
-        }
+__device__ __forceinline__ bool sphere_candidate(const float4 s, V3 o, V3 d, float& t) {
+    const V3 oc = mk(A::sub(s.x, o.x), A::sub(s.y, o.y), A::sub(s.z, o.z));
+    const float b = dot<A>(oc, d);
+    const float c = A::sub(dot<A>(oc, oc), s.w);
+    const float dis = A::msub(b, b, c);
+    if (!(dis > 0.0f)) return false;
+    const float sq = A::sqrt(dis);
+    t = A::sub(b, sq);
+    if (!in_range(t)) t = A::add(b, sq);
+    return t >= RT_T_MIN;
+}
+// cl:196-255: intersection of two balls.  Every accepted branch yields t >= T_MIN; t <= T_MAX (cl:245) is implied
+// by the caller's best-so-far test.
+template <class A>
+__device__ __forceinline__ bool lens_candidate(const float4 l1, const float4 l2, V3 o, V3 d, float& t, uint32_t& side) {
+    V3 oc = mk(A::sub(l1.x, o.x), A::sub(l1.y, o.y), A::sub(l1.z, o.z));
+    const float b1 = dot<A>(oc, d);
+    const float dis1 = A::msub(b1, b1, A::sub(dot<A>(oc, oc), l1.w));
+    oc = mk(A::sub(l2.x, o.x), A::sub(l2.y, o.y), A::sub(l2.z, o.z));
+    const float b2 = dot<A>(oc, d);
+    const float dis2 = A::msub(b2, b2, A::sub(dot<A>(oc, oc), l2.w));
+    if (!(dis1 > 0.0f && dis2 > 0.0f)) return false;
+    const float d1 = A::sqrt(dis1), d2 = A::sqrt(dis2);
+    const float t1A = A::sub(b1, d1), t1B = A::add(b1, d1), t2A = A::sub(b2, d2), t2B = A::add(b2, d2);
+    t = -1.0f;
+    side = 0u;
+    if ((t1B < t2A) || (t2B < t1A)) { /* misses the intersection of the two balls, cl:220 */ }
+    else if (RT_T_MIN <= t1A || RT_T_MIN <= t2A) {          // outside, cl:221-231
+        if (t2A <= t1A) { side = 0u; t = t1A; } else { side = 1u; t = t2A; }
+    } else if (RT_T_MIN <= t1B && RT_T_MIN <= t2B) {        // inside, cl:232-242
+        if (t1B <= t2B) { side = 0u; t = t1B; } else { side = 1u; t = t2B; }
     }
+    return t >= RT_T_MIN;
+}
+template <class A>
+__device__ __forceinline__ void hit_planes(const DevScene& sc, const float4* __restrict__ S, V3 o, V3 d, Hit& best) {
 #pragma unroll 1
     for (uint32_t i = 0; i < sc.n_pla; ++i) {                       // cl:176-194
         const float4 p = S[sc.off_pla + 2 * i], n4 = S[sc.off_pla + 2 * i + 1];
@@ -81,28 +102,19 @@ __device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* _
         const float t = A::div(b, a);
         if (t >= RT_T_MIN && t < best.t) { best.t = t; best.id = (kKindPlane << 28) | i; }
     }
+}
+template <class A>
+__device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* __restrict__ S, V3 o, V3 d, Hit& best) {
+    for (uint32_t i = 0; i < sc.n_sph; ++i) {
+        float t;
+        if (sphere_candidate<A>(S[i], o, d, t) && t < best.t) { best.t = t; best.id = (kKindSphere << 28) | i; }
+    }
+    hit_planes<A>(sc, S, o, d, best);
 #pragma unroll 1
-    for (uint32_t i = 0; i < sc.n_len; ++i) {                       // cl:196-255
-        const float4 l1 = S[sc.off_len + 2 * i], l2 = S[sc.off_len + 2 * i + 1];
-        V3 oc = mk(A::sub(l1.x, o.x), A::sub(l1.y, o.y), A::sub(l1.z, o.z));
-        const float b1 = dot<A>(oc, d);
-        const float dis1 = A::msub(b1, b1, A::sub(dot<A>(oc, oc), l1.w));
-        oc = mk(A::sub(l2.x, o.x), A::sub(l2.y, o.y), A::sub(l2.z, o.z));
-        const float b2 = dot<A>(oc, d);
-        const float dis2 = A::msub(b2, b2, A::sub(dot<A>(oc, oc), l2.w));
-        if (dis1 > 0.0f && dis2 > 0.0f) {
-            const float d1 = A::sqrt(dis1), d2 = A::sqrt(dis2);
-            const float t1A = A::sub(b1, d1), t1B = A::add(b1, d1), t2A = A::sub(b2, d2), t2B = A::add(b2, d2);
-            float t = -1.0f;
-            uint32_t side = 0u;
-            if ((t1B < t2A) || (t2B < t1A)) { /* misses the intersection of the two balls, cl:220 */ }
-            else if (RT_T_MIN <= t1A || RT_T_MIN <= t2A) {          // outside, cl:221-231
-                if (t2A <= t1A) { side = 0u; t = t1A; } else { side = 1u; t = t2A; }
-            } else if (RT_T_MIN <= t1B && RT_T_MIN <= t2B) {        // inside, cl:232-242
-                if (t1B <= t2B) { side = 0u; t = t1B; } else { side = 1u; t = t2B; }
-            }
-            // every accepted branch yields t >= T_MIN; t <= T_MAX (cl:245) is implied by t < best.t
-            if (t >= RT_T_MIN && t < best.t) { best.t = t; best.id = (kKindLens << 28) | i; best.aux = side; }
+    for (uint32_t i = 0; i < sc.n_len; ++i) {
+        float t; uint32_t side;
+        if (lens_candidate<A>(S[sc.off_len + 2 * i], S[sc.off_len + 2 * i + 1], o, d, t, side) && t < best.t) {
+            best.t = t; best.id = (kKindLens << 28) | i; best.aux = side;
         }
     }
 }
@@ -163,6 +175,85 @@ static __device__ __noinline__ Hit nearest_hit_exact_cold(const DevScene& sc, co
                                                           float dx, float dy, float dz, uint32_t mesh_mode) {
     Hit best;
     nearest_hit_lane<Exact>(sc, S, mk(ox, oy, oz), mk(dx, dy, dz), mesh_mode, best);
+    return best;
+}
+
+// ---------------------------------------------------------------------------------- LBVH traversal
+// Nearest hit over the finite primitives through the GPU-built LBVH (rt_bvh.cu).  Candidates arrive in traversal
+// order, not in hitScene order, so acceptance is by (t, id) lexicographic order — id = kind << 28 | index grows in
+// hitScene's scan order (spheres, planes, lenses, triangles; index order inside a kind), which reproduces "on equal t
+// the earlier one wins" (strict < at cl:328-352).  Meshes use the nearest-front-facing rule (RT_MESH_NEAREST): the
+// reference's first-front-facing-in-face-order rule (cl:291-303) depends on the scan order and cannot be answered by
+// a spatial hierarchy.  Box tests are conservative (boxes padded at build time, exit distance scaled up), the
+// primitive tests are the same policy-A routines as in the brute-force path, so the winner equals brute force.
+__device__ __forceinline__ bool closer(float t, uint32_t id, const Hit& best) {
+    return t < best.t || (t == best.t && t < RT_T_MAX && id < best.id);
+}
+template <class A>
+__device__ __forceinline__ void bvh_leaf(const DevScene& sc, const float4* __restrict__ S, const uint2 lf, V3 o, V3 d, Hit& best) {
+    const uint32_t kind = lf.x >> 28;
+    if (kind == kKindSphere) {
+        float t;
+        if (sphere_candidate<A>(__ldg(S + lf.y), o, d, t) && closer(t, lf.x, best)) { best.t = t; best.id = lf.x; best.aux = 0u; }
+    } else if (kind == kKindLens) {
+        float t; uint32_t side;
+        if (lens_candidate<A>(__ldg(S + sc.off_len + 2 * lf.y), __ldg(S + sc.off_len + 2 * lf.y + 1), o, d, t, side) && closer(t, lf.x, best)) {
+            best.t = t; best.id = lf.x; best.aux = side;
+        }
+    } else {
+        const float4* T = S + sc.off_tri + 3 * lf.y;
+        float t, u, v;
+        if (front_facing<A>(T, d) && hit_triangle<A>(T, o, d, t, u, v) && closer(t, lf.x, best)) {
+            best.t = t; best.id = lf.x; best.bu = u; best.bv = v; best.aux = lf.y;
+        }
+    }
+}
+__device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near) {
+    const float ax = (lo[0] - o.x) * inv.x, bx = (hi[0] - o.x) * inv.x;
+    const float ay = (lo[1] - o.y) * inv.y, by = (hi[1] - o.y) * inv.y;
+    const float az = (lo[2] - o.z) * inv.z, bz = (hi[2] - o.z) * inv.z;
+    t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
+    return t_near <= t_far && t_near <= t_best;
+}
+template <class A>
+__device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
+    if (bvh.n_leaves == 0u) return;
+    if (bvh.root < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~bvh.root)), o, d, best); return; }
+    const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    int stack[64];
+    int sp = 0, node = bvh.root;
+    for (;;) {
+        const float4* N = reinterpret_cast<const float4*>(bvh.nodes + node);
+        const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+        const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
+        const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
+        float t0, t1;
+        bool h0 = slab(lo0, hi0, o, inv, best.t, t0), h1 = slab(lo1, hi1, o, inv, best.t, t1);
+        if (h0 && c0 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c0)), o, d, best); h0 = false; }
+        if (h1 && c1 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c1)), o, d, best); h1 = false; }
+        if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
+            const bool first0 = t0 <= t1;
+            if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+            node = first0 ? c0 : c1;
+        } else if (h0) node = c0;
+        else if (h1) node = c1;
+        else {
+            if (sp == 0) break;
+            node = stack[--sp];
+        }
+    }
+}
+template <class A>
+__device__ __forceinline__ void nearest_hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
+    best.t = RT_T_MAX; best.id = kIdMiss; best.bu = 0.0f; best.bv = 0.0f; best.aux = 0u;
+    hit_planes<A>(sc, S, o, d, best);
+    hit_bvh<A>(sc, S, bvh, o, d, best);
+}
+static __device__ __noinline__ Hit nearest_hit_exact_cold_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh,
+                                                              float ox, float oy, float oz, float dx, float dy, float dz) {
+    Hit best;
+    nearest_hit_bvh<Exact>(sc, S, bvh, mk(ox, oy, oz), mk(dx, dy, dz), best);
     return best;
 }
 
@@ -493,11 +584,17 @@ __device__ __forceinline__ V3 primary_dir(const float* cam, int x, int y, int W,
 // One lane owns one pixel; warps cover 8x4 pixel tiles.  Lanes are persistent over samples: the moment a
 // path ends the lane accumulates it and restarts from the primary ray, so each trip of the while loop is one
 // nearest-hit query executed by every lane that still has samples left.
-template <class A>
+// BVH = false: brute force over the shared-memory copy of the scene (small scenes);
+// BVH = true : planes brute force + LBVH traversal, scene data read from global memory (large scenes).
+template <class A, bool BVH>
 __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
-    stage_scene(p.sc, smem);
-    const float4* S = smem;
-    uint8_t* list = warp_list(p.sc, smem);
+    const float4* S = p.sc.stream;
+    uint8_t* list = nullptr;
+    if (!BVH) {
+        stage_scene(p.sc, smem);
+        S = smem;
+        list = warp_list(p.sc, smem);
+    }
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tiles_x = (p.W + 7) >> 3;
@@ -525,10 +622,12 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
     while (__any_sync(RT_FULL, k < k_end)) {
         const bool active = k < k_end;
         Hit h;
-        nearest_hit_warp<A>(p.sc, S, list, o, d, active, p.mesh_mode, h);
+        if (BVH) { if (active) nearest_hit_bvh<A>(p.sc, S, p.bvh, o, d, h); }
+        else nearest_hit_warp<A>(p.sc, S, list, o, d, active, p.mesh_mode, h);
         if (active) {
-            if (!A::kExact && p.certify_id && i == 0u && h.id != certified)
-                h = nearest_hit_exact_cold(p.sc, S, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);   // knife-edge pixel: take the exact primary hit
+            if (!A::kExact && p.certify_id && i == 0u && h.id != certified)   // knife-edge pixel: take the exact primary hit
+                h = BVH ? nearest_hit_exact_cold_bvh(p.sc, S, p.bvh, o.x, o.y, o.z, d.x, d.y, d.z)
+                        : nearest_hit_exact_cold(p.sc, S, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);
             ++rays;
             bool ended;
             if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }   // cl:450-452
@@ -556,10 +655,11 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
 
 // Nearest hit of arbitrary rays (rays6 != nullptr) or of the primary rays of the frame; same code path as the
 // render loop (warp-cooperative meshes, optional certification of primary hits).
-template <class A>
-__device__ __forceinline__ void probe_hits_body(const ProbeLaunch& p, float4* smem) {
-    stage_scene(p.sc, smem);
-    uint8_t* list = warp_list(p.sc, smem);
+template <class A, bool BVH>
+__device__ __forceinline__ void probe_hits_body(const ProbeLaunch& p, float4* smem_) {
+    const float4* smem = p.sc.stream;
+    uint8_t* list = nullptr;
+    if (!BVH) { stage_scene(p.sc, smem_); smem = smem_; list = warp_list(p.sc, smem_); }
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = i < p.n;
     V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f);
@@ -573,18 +673,22 @@ __device__ __forceinline__ void probe_hits_body(const ProbeLaunch& p, float4* sm
         }
     }
     Hit h;
-    nearest_hit_warp<A>(p.sc, smem, list, o, d, active, p.mesh_mode, h);
+    if (BVH) { if (active) nearest_hit_bvh<A>(p.sc, smem, p.bvh, o, d, h); }
+    else nearest_hit_warp<A>(p.sc, smem, list, o, d, active, p.mesh_mode, h);
     if (!active) return;
-    if (!A::kExact && p.certify_id && h.id != p.certify_id[i]) h = nearest_hit_exact_cold(p.sc, smem, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);
+    if (!A::kExact && p.certify_id && h.id != p.certify_id[i])
+        h = BVH ? nearest_hit_exact_cold_bvh(p.sc, smem, p.bvh, o.x, o.y, o.z, d.x, d.y, d.z)
+                : nearest_hit_exact_cold(p.sc, smem, o.x, o.y, o.z, d.x, d.y, d.z, p.mesh_mode);
     if (p.out_id) p.out_id[i] = h.id;
     if (p.out_t) p.out_t[i] = h.t;
 }
 
 // One iteration of the path loop per ray (single-bounce differential test).
-template <class A>
-__device__ __forceinline__ void probe_bounce_body(const ProbeLaunch& p, float4* smem) {
-    stage_scene(p.sc, smem);
-    uint8_t* list = warp_list(p.sc, smem);
+template <class A, bool BVH>
+__device__ __forceinline__ void probe_bounce_body(const ProbeLaunch& p, float4* smem_) {
+    const float4* smem = p.sc.stream;
+    uint8_t* list = nullptr;
+    if (!BVH) { stage_scene(p.sc, smem_); smem = smem_; list = warp_list(p.sc, smem_); }
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = i < p.n;
     V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f);
@@ -593,7 +697,8 @@ __device__ __forceinline__ void probe_bounce_body(const ProbeLaunch& p, float4* 
         d = mk(p.rays6[6 * i + 3], p.rays6[6 * i + 4], p.rays6[6 * i + 5]);
     }
     Hit h;
-    nearest_hit_warp<A>(p.sc, smem, list, o, d, active, p.mesh_mode, h);
+    if (BVH) { if (active) nearest_hit_bvh<A>(p.sc, smem, p.bvh, o, d, h); }
+    else nearest_hit_warp<A>(p.sc, smem, list, o, d, active, p.mesh_mode, h);
     if (!active) return;
     V3 out = mk(1.0f, 1.0f, 1.0f);
     const PixelRng pr = make_pixel_rng(p.gx[i], p.gy[i], (uint32_t)p.W, p.seed);
@@ -612,8 +717,8 @@ inline size_t staged_bytes(const DevScene& sc) {
 }
 
 template <class K, class P>
-inline cudaError_t launch_staged(K kernel, const P& p, size_t work_items, cudaStream_t s) {
-    const size_t smem = staged_bytes(p.sc);
+inline cudaError_t launch_staged(K kernel, const P& p, size_t work_items, cudaStream_t s, bool bvh = false) {
+    const size_t smem = bvh ? 0 : staged_bytes(p.sc);
     if (smem > kMaxStagedBytes) return cudaErrorInvalidValue;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

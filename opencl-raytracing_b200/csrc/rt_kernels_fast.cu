@@ -8,20 +8,33 @@
 namespace rtb {
 extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_trace_fast(const __grid_constant__ TraceLaunch p) {
     extern __shared__ float4 smem[];
-    trace_body<Fused>(p, smem);
+    trace_body<Fused, false>(p, smem);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_fast_bvh(const __grid_constant__ TraceLaunch p) {
+    trace_body<Fused, true>(p, nullptr);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
-    probe_hits_body<Fused>(p, smem);
+    probe_hits_body<Fused, false>(p, smem);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast_bvh(const __grid_constant__ ProbeLaunch p) {
+    probe_hits_body<Fused, true>(p, nullptr);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_bounce_fast(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
-    probe_bounce_body<Fused>(p, smem);
+    probe_bounce_body<Fused, false>(p, smem);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_bounce_fast_bvh(const __grid_constant__ ProbeLaunch p) {
+    probe_bounce_body<Fused, true>(p, nullptr);
 }
 cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s) {
     const size_t tiles = (size_t)((p.W + 7) / 8) * ((p.H + 3) / 4);
-    return launch_staged(k_trace_fast, p, tiles * 32, s);
+    return p.bvh.n_leaves ? launch_staged(k_trace_fast_bvh, p, tiles * 32, s, true) : launch_staged(k_trace_fast, p, tiles * 32, s);
 }
-cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) { return launch_staged(k_probe_hits_fast, p, p.n, s); }
-cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s) { return launch_staged(k_probe_bounce_fast, p, p.n, s); }
+cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) {
+    return p.bvh.n_leaves ? launch_staged(k_probe_hits_fast_bvh, p, p.n, s, true) : launch_staged(k_probe_hits_fast, p, p.n, s);
+}
+cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s) {
+    return p.bvh.n_leaves ? launch_staged(k_probe_bounce_fast_bvh, p, p.n, s, true) : launch_staged(k_probe_bounce_fast, p, p.n, s);
+}
 }  // namespace rtb

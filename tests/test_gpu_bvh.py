@@ -1,0 +1,121 @@
+"""GPU tests of the LBVH path: it must return the SAME nearest hit as brute force (north_star): same id, same t bits,
+ties resolved like hitScene's scan order.  Checked against (a) the brute-force kernels on scenes small enough for
+shared memory, (b) the oracle's brute force (nearest-front-facing mesh rule) on larger scenes, (c) whole images."""
+import numpy as np
+import pytest
+
+import oracle_py as op
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def random_rays(n, seed, box=((-14, -8, -2), (14, 3, 45))):
+    rng = np.random.RandomState(seed)
+    o = rng.uniform(box[0], box[1], (n, 3)).astype(np.float32)
+    v = rng.normal(size=(n, 3))
+    v = (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+    return np.concatenate([o, v], 1)
+
+
+def ctx_for(rt, arrays, W=64, H=64, **prm):
+    ctx = rt.Context(W, H)
+    ctx.set_params(**prm)
+    ctx.upload_scene(arrays)
+    return ctx
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+def test_bvh_equals_brute_force_kernels(arith):
+    import rtb200 as rt
+    from rtb200 import synth
+    arrays, info = synth.scene(n_spheres=300, mesh_subdiv=3, seed=5)       # 1280 triangles: fits shared memory
+    rays = random_rays(60000, 1)
+    A = getattr(rt, "ARITH_" + arith.upper())
+    with ctx_for(rt, arrays, arith=A, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BRUTE) as b, \
+         ctx_for(rt, arrays, arith=A, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BVH) as v:
+        ib, tb = b.trace_rays(rays)
+        iv, tv = v.trace_rays(rays)
+        assert b.stats().bvh_nodes == 0 and v.stats().bvh_nodes == info["spheres"] + info["triangles"] - 1
+    assert (ib != rt.ID_MISS).mean() > 0.3 and len(np.unique(ib >> 28)) >= 3
+    assert np.array_equal(ib, iv)
+    assert np.array_equal(bits(tb), bits(tv))
+
+
+def test_bvh_ties_follow_scan_order():
+    """Coincident primitives: the lower index / earlier kind must win, as strict < in hitScene gives."""
+    import rtb200 as rt
+    from rtb200 import synth
+    mats = synth.materials([(synth.T_DIFFUSE, (1, 1, 1), 1)])
+    sph = np.zeros(700, synth.SPHERE_DT)
+    for i in range(700):
+        k = i // 2                                                         # every sphere exists twice
+        sph[i] = ((float(k % 25) * 2.5 - 30, float(k // 25) * 2.5 - 17, 20.0, 0), 1.0, 0)
+    arrays = {"materials": synth._bytes(mats), "spheres": synth._bytes(sph), "planes": np.zeros((0, 48), np.uint8),
+              "lenses": np.zeros((0, 64), np.uint8), "vertices": np.zeros((0, 16), np.uint8), "uvs": np.zeros((0, 8), np.uint8),
+              "indices": np.zeros((0, 4), np.uint8), "meshes": np.zeros((0, 16), np.uint8), "models": np.zeros((0, 12), np.uint8)}
+    rays = random_rays(20000, 3, box=((-30, -17, 0), (30, 17, 1)))
+    rays[:, 3:] = (0, 0, 1)
+    with ctx_for(rt, arrays, arith=rt.ARITH_STRICT, accel=rt.ACCEL_BVH) as v, ctx_for(rt, arrays, arith=rt.ARITH_STRICT, accel=rt.ACCEL_BRUTE) as b:
+        iv, tv = v.trace_rays(rays)
+        ib, tb = b.trace_rays(rays)
+    hit = iv != rt.ID_MISS
+    assert hit.mean() > 0.2
+    assert np.all((iv[hit] & 1) == 0)                                      # the even (first) copy always wins
+    assert np.array_equal(iv, ib) and np.array_equal(bits(tv), bits(tb))
+
+
+def test_bvh_equals_oracle_brute_force_large(port):
+    import rtb200 as rt
+    from rtb200 import synth
+    arrays, info = synth.scene(n_spheres=500, mesh_subdiv=5, seed=9)       # 20 480 triangles: BVH only
+    rays = random_rays(4000, 2)
+    aim = np.array([0.0, -1.0, 9.0]) + np.random.RandomState(4).normal(size=(2000, 3)) * 2.0 - rays[:2000, :3]   # half aimed at the mesh
+    rays[:2000, 3:] = (aim / np.linalg.norm(aim, axis=1, keepdims=True)).astype(np.float32)
+    d = op.make_desc(arrays)
+    want = [port.intersect(d, r[:3], r[3:], op.MESH_NEAREST)[1] for r in rays]
+    want_id = np.array([h.id for h in want], np.uint32)
+    want_t = np.array([h.t for h in want], np.float32)
+    with ctx_for(rt, arrays, arith=rt.ARITH_STRICT, mesh_mode=rt.MESH_NEAREST) as ctx:     # RT_ACCEL_AUTO picks the BVH
+        ids, ts = ctx.trace_rays(rays)
+        assert ctx.stats().bvh_nodes == info["spheres"] + info["triangles"] - 1
+        with pytest.raises(rt.RtError):                                    # brute force does not fit shared memory
+            ctx.set_params(arith=rt.ARITH_STRICT, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BRUTE)
+            ctx.trace_rays(rays)
+        ctx.set_params(arith=rt.ARITH_STRICT, mesh_mode=rt.MESH_FIRST_FRONT)
+        with pytest.raises(rt.RtError):                                    # the BVH cannot answer the scan-order rule
+            ctx.trace_rays(rays)
+    assert (want_id >> 28 == 4).mean() > 0.1
+    assert np.array_equal(ids, want_id) and np.array_equal(bits(ts), bits(want_t))
+
+
+def test_bvh_image_bit_exact_and_certified(port):
+    """Whole pipeline through the LBVH kernels: strict image == oracle bits; fast primary ids identical."""
+    import rtb200 as rt
+    from rtb200 import fixtures as fx, synth
+    arrays, _ = synth.scene(n_spheres=400, mesh_subdiv=4, seed=11)
+    W, H, spp, depth = 160, 100, 4, 10
+    cam = fx.camera(60, W / H)
+    d = op.make_desc(arrays)
+    prm = port.params(max_depth=depth, rng_mode=op.RNG_COUNTER, seed=21, mesh_mode=op.MESH_NEAREST)
+    want, rays_want, _ = port.render(d, None, cam, None, W, H, 0, spp, prm)
+    want_ids, _ = port.primary_ids(d, cam, W, H, op.MESH_NEAREST)
+    with rt.Context(W, H) as ctx:
+        ctx.set_params(max_depth=depth, rng_mode=rt.RNG_COUNTER, seed=21, arith=rt.ARITH_STRICT, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BVH)
+        ctx.upload_scene(arrays)
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        got = ctx.read_image()
+        assert int((bits(got) != bits(want)).any(-1).sum()) <= 2
+        assert abs(int(ctx.stats().rays_last) - int(rays_want)) <= 20
+        ids, _ = ctx.primary_ids(cam)
+        assert np.array_equal(ids, want_ids)
+        ctx.set_params(max_depth=depth, rng_mode=rt.RNG_COUNTER, seed=21, arith=rt.ARITH_FAST, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BVH)
+        ids_f, _ = ctx.primary_ids(cam)
+        assert np.array_equal(ids_f, want_ids)
+        ctx.render_samples(cam, 0, 16, rt.ACCUM_REFERENCE)
+        fast = ctx.read_image()
+    w16, _, _ = port.render(d, None, cam, None, W, H, 0, 16, prm)
+    assert abs(float((fast[..., :3] ** 2).mean()) - float((w16[..., :3] ** 2).mean())) < 5e-3
