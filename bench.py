@@ -24,6 +24,8 @@ sys.path.insert(0, os.path.join(ROOT, "opencl-raytracing_b200"))
 
 W, H, SPP, DEPTH = 1920, 1080, 1024, 30
 TABLE_SEED = 12345
+MESH_MODE = 0          # RT_MESH_FIRST_FRONT (the reference's rule); the LBVH configs use RT_MESH_NEAREST
+CONFIG = "c2"
 SLOTS_PER_RAY = 867.0   # measured FP32 issue slots per ray of the reference algorithm, default scene
 METRIC = "Mrays/s at 1080p per scene, 1/2/4/8 B200, vs reference OpenCL on host CPU"
 WORKLOAD = "C2: default scene (8 spheres, 1 plane, 1 lens, 2 textured cubes = 24 triangles), 1920x1080, 1024 spp, max depth 30"
@@ -35,11 +37,36 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--spp", type=int, default=SPP)
+    ap.add_argument("--spp", type=int, default=None)
     ap.add_argument("--arith", default="fast", choices=["fast", "strict"])
     ap.add_argument("--rng", default="counter", choices=["counter", "table"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"],
+                    help="BASELINE.json configs; the driver's default (and the headline) is c2")
     return ap.parse_args()
+
+
+def select_config(a):
+    """c2 is the bench line; the other BASELINE configs are reported with the same code for DESIGN.md."""
+    global W, H, SPP, DEPTH, WORKLOAD, MESH_MODE, CONFIG, SLOTS_PER_RAY
+    CONFIG = a.config
+    if a.config == "c1":
+        W, H, SPP, DEPTH = 800, 600, 16, 8
+        WORKLOAD = "C1: default scene, 800x600, 16 spp, max depth 8"
+    elif a.config == "c3":
+        W, H, SPP, DEPTH = 1920, 1080, 4096, 30
+        WORKLOAD = "C3: reference cube meshes (textured) + diffuse/dielectric/reflective spheres, 1920x1080, 4096 spp, max depth 30"
+        SLOTS_PER_RAY = None
+    elif a.config == "c4":
+        W, H, SPP, DEPTH, MESH_MODE = 3840, 2160, 64, 30, 1
+        WORKLOAD = "C4: synthetic closed mesh of 1 310 720 triangles + 1001 spheres + floor plane, 3840x2160, GPU-built LBVH, max depth 30"
+        SLOTS_PER_RAY = None
+    elif a.config == "c5":
+        W, H, SPP, DEPTH, MESH_MODE = 3840, 2160, 64, 16, 1
+        WORKLOAD = "C5: 100 001 mixed-material spheres + floor plane, 3840x2160, GPU-built LBVH, max depth 16"
+        SLOTS_PER_RAY = None
+    if a.spp is None:
+        a.spp = SPP
 
 
 class ClockSampler:
@@ -92,8 +119,14 @@ class ClockSampler:
 def load_inputs():
     import rtb200
     from rtb200 import fixtures as fx
-    arr, tex8 = fx.default_scene()
-    tex = fx.textures_to_float(tex8)
+    if CONFIG in ("c4", "c5"):
+        import numpy as np
+        from rtb200 import synth
+        arr, _ = synth.c4_scene(subdiv=8) if CONFIG == "c4" else synth.c5_scene()
+        tex = np.zeros((1, 1, 1, 4), np.float32)
+    else:
+        arr, tex8 = fx.c3_scene() if CONFIG == "c3" else fx.default_scene()
+        tex = fx.textures_to_float(tex8)
     cam = fx.camera(60, W / H)
     table = rtb200.make_random_table(TABLE_SEED)
     return arr, tex, cam, table
@@ -165,8 +198,8 @@ def main_b200(a):
 
     arr, tex, cam, table = load_inputs()
     ctx = rtb200.Context(W, H, local)
+    ctx.set_params(max_depth=DEPTH, rng_mode=rng, seed=1, arith=arith, mesh_mode=MESH_MODE)
     ctx.upload_textures(tex); ctx.upload_scene(arr); ctx.set_random_table(table)
-    ctx.set_params(max_depth=DEPTH, rng_mode=rng, seed=1, arith=arith)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
@@ -262,7 +295,7 @@ def main_b200(a):
             pass
         k_ms = sum(kernel_ms) / len(kernel_ms)
         rays_launch = rays_steps[0]
-        achieved = SLOTS_PER_RAY * rays_launch / (k_ms * 1e-3) / 1e9
+        achieved = (SLOTS_PER_RAY or 0.0) * rays_launch / (k_ms * 1e-3) / 1e9
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_bytes = 2.0 * W * H * 16          # accumulation buffer read + write, once per launch
         out = {
@@ -280,7 +313,7 @@ def main_b200(a):
                             "rt_render_samples, reduce, rt_finalize, rt_read_image to host, every step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32_issue", "achieved": round(achieved, 1), "peak": round(peak_gslots, 1),
-                         "unit": "G lane-slots/s", "frac": round(achieved / peak_gslots, 4) if peak_gslots else None,
+                         "unit": "G lane-slots/s", "frac": round(achieved / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
                          "traffic": None, "kernel": "k_trace_%s" % a.arith, "kernel_ms": round(k_ms, 3),
                          "slots_per_ray": SLOTS_PER_RAY, "rays_per_launch": int(rays_launch),
                          "peak_source": "measured live: dependent-free FFMA loop on all SMs (rt_measure_fp32_peak); "
@@ -288,7 +321,8 @@ def main_b200(a):
                          "hbm": {"achieved_gbs": round(alg_bytes / (k_ms * 1e-3) / 1e9, 2), "peak_gbs": hbm_peak,
                                  "note": "evidence only: 33 MB per launch, not the bound"}},
         }
-        if world == 1 and not a.no_cpu_baseline:
+        out["config"]["bvh_nodes"] = int(ctx.stats().bvh_nodes)
+        if world == 1 and not a.no_cpu_baseline and CONFIG in ("c1", "c2", "c3"):
             rate, cores, kind, rays, secs, _ = cpu_reference_rate(4, 4, 1)
             out["cpu_baseline"] = {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind,
                                    "sample": "%dx%d, 16 timed spp in 4 steps (one pass per sample), depth %d, %.1f s of CPU work"
@@ -300,6 +334,7 @@ def main_b200(a):
 
 if __name__ == "__main__":
     args = parse()
+    select_config(args)
     if args.impl == "reference":
         main_reference(args)
     else:

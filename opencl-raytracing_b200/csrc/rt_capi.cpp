@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <string>
@@ -475,6 +476,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     { int r = ensure_accel(c); if (r != RT_OK) return r; }
     TraceLaunch L{};
     L.bvh = dev_bvh(c);
+    { const char* e = std::getenv("RTB200_BVH_REGEN"); L.bvh_regen = e ? (uint32_t)std::atoi(e) : 0u; }
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     std::memcpy(L.cam, cam, 12 * sizeof(float));
     L.W = c->W; L.H = c->H; L.first = first; L.n = n; L.depth = c->prm.max_depth;

@@ -67,6 +67,7 @@ struct TraceLaunch {
     unsigned long long* rays;  // device counter
     const uint32_t* certify_id; // fast arithmetic: Exact primary-hit id per pixel (nullptr = no certification)
     DevBvh bvh;                // n_leaves == 0: brute-force path over the staged scene
+    uint32_t bvh_regen;        // LBVH kernel: waiting lanes that trigger a shading/regeneration phase (0 = default 8)
 };
 
 struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays

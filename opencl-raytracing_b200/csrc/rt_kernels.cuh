@@ -653,6 +653,107 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
     if (lane == 0 && rays) atomicAdd(p.rays, rays);
 }
 
+// LBVH render kernel.  Traversal lengths differ wildly between rays (tens to hundreds of nodes), so running one whole
+// query per trip — as the brute-force kernel does — leaves most lanes idle (measured: 4.9 of 32 lanes active).  Here
+// the main loop advances every lane by ONE node per trip; a lane whose traversal is finished waits until at least
+// `regen` lanes are waiting (or nobody traverses any more), then the waiting lanes shade, bounce or regenerate the
+// next sample's primary ray, and re-enter the traversal loop (persistent lanes with in-loop ray fetch).
+template <class A>
+__device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
+    const float4* S = p.sc.stream;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tiles_x = (p.W + 7) >> 3;
+    const int tile = blockIdx.x * (kTraceThreads / 32) + warp;
+    const int x = (tile % tiles_x) * 8 + (lane & 7);
+    const int y = (tile / tiles_x) * 4 + (lane >> 3);
+    const bool live = (x < p.W) && (y < p.H);
+
+    const V3 cam_o = mk(p.cam[0], p.cam[1], p.cam[2]);
+    const V3 d0 = primary_dir<Exact>(p.cam, x, y, p.W, p.H);
+    const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
+    ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
+    float4* px = p.target + (size_t)y * p.W + x;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    uint32_t certified = kIdMiss;
+    if (live) {
+        if (p.accum_mode == 1u || p.first > 0u) acc = *px;
+        if (!A::kExact && p.certify_id) certified = __ldg(p.certify_id + (size_t)y * p.W + x);
+    }
+    const uint32_t k_end = p.first + p.n;
+    uint32_t k = live ? p.first : k_end, i = 0u;
+    V3 o = cam_o, d = d0, out = mk(1.0f, 1.0f, 1.0f);
+    unsigned long long rays = 0ull;
+    const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
+
+    Hit h;
+    V3 inv = mk(0.0f, 0.0f, 0.0f);
+    int stack[64];
+    int sp = 0, node = 0;
+    bool traversing = false;
+    auto start_ray = [&]() {
+        h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
+        hit_planes<A>(p.sc, S, o, d, h);
+        sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
+        if (traversing && node < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~node)), o, d, h); traversing = false; }
+        inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    };
+    bool has_ray = k < k_end;
+    if (has_ray) start_ray();
+
+    while (__any_sync(RT_FULL, has_ray)) {
+        for (;;) {                                           // ---- traversal: one node per trip
+            if (traversing) {
+                const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
+                const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+                const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
+                const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
+                float t0, t1;
+                bool h0 = slab(lo0, hi0, o, inv, h.t, t0), h1 = slab(lo1, hi1, o, inv, h.t, t1);
+                if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
+                if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
+                if (h0 && h1) {
+                    const bool first0 = t0 <= t1;
+                    if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+                    node = first0 ? c0 : c1;
+                } else if (h0) node = c0;
+                else if (h1) node = c1;
+                else if (sp > 0) node = stack[--sp];
+                else traversing = false;
+            }
+            const unsigned trav = __ballot_sync(RT_FULL, traversing);
+            const unsigned waiting = __ballot_sync(RT_FULL, has_ray && !traversing);
+            if (trav == 0u || (uint32_t)__popc(waiting) >= regen) break;
+        }
+        if (has_ray && !traversing) {                        // ---- shading / regeneration for the waiting lanes
+            if (!A::kExact && p.certify_id && i == 0u && h.id != certified)
+                h = nearest_hit_exact_cold_bvh(p.sc, S, p.bvh, o.x, o.y, o.z, d.x, d.y, d.z);
+            ++rays;
+            bool ended;
+            if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }
+            else ended = shade<A>(env, S, h, pr, o, d, out, k, i);
+            ++i;
+            if (ended || i >= p.depth) {
+                if (p.accum_mode == 1u) {
+                    acc.x = A::add(acc.x, out.x); acc.y = A::add(acc.y, out.y); acc.z = A::add(acc.z, out.z); acc.w += 1.0f;
+                } else if (k == 0u) {
+                    acc = make_float4(A::sqrt(out.x), A::sqrt(out.y), A::sqrt(out.z), 1.0f);
+                } else {
+                    const float a = A::div((float)k, (float)(k + 1u));
+                    const float pr_ = A::mul(acc.x, acc.x), pg_ = A::mul(acc.y, acc.y), pb_ = A::mul(acc.z, acc.z);
+                    acc = make_float4(A::sqrt(A::mad(A::sub(pr_, out.x), a, out.x)), A::sqrt(A::mad(A::sub(pg_, out.y), a, out.y)),
+                                      A::sqrt(A::mad(A::sub(pb_, out.z), a, out.z)), 1.0f);
+                }
+                ++k; i = 0u; o = cam_o; d = d0; out = mk(1.0f, 1.0f, 1.0f);
+            }
+            has_ray = k < k_end;
+            if (has_ray) start_ray();
+        }
+    }
+    if (live) *px = acc;
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(RT_FULL, rays, off);
+    if (lane == 0 && rays) atomicAdd(p.rays, rays);
+}
+
 // Nearest hit of arbitrary rays (rays6 != nullptr) or of the primary rays of the frame; same code path as the
 // render loop (warp-cooperative meshes, optional certification of primary hits).
 template <class A, bool BVH>

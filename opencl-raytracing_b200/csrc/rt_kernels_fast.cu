@@ -11,7 +11,7 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_tra
     trace_body<Fused, false>(p, smem);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_fast_bvh(const __grid_constant__ TraceLaunch p) {
-    trace_body<Fused, true>(p, nullptr);
+    trace_body_bvh<Fused>(p);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];

@@ -8,7 +8,7 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_strict(const
     trace_body<Exact, false>(p, smem);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_strict_bvh(const __grid_constant__ TraceLaunch p) {
-    trace_body<Exact, true>(p, nullptr);
+    trace_body_bvh<Exact>(p);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_strict(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
