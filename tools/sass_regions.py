@@ -28,7 +28,7 @@ def region(ln):
 rows = list(csv.reader(open(ncu_csv))); hdr = rows[1]; data = [r for r in rows[2:] if len(r) > 10]
 iE, iT = hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 lines = open(dis).read().split("\n")
-start = [i for i, l in enumerate(lines) if l.strip().startswith(".section") and (".text." + kernel) in l][0]
+start = [i for i, l in enumerate(lines) if l.strip().startswith(".section") and (".text." + kernel + ",") in l][0]
 cur = None; last = None; k = 0; reg = collections.Counter(); regt = collections.Counter(); tot = 0
 for l in lines[start + 1:]:
     if l.strip().startswith(".section"): break
