@@ -49,6 +49,8 @@ enum { RT_ACCUM_REFERENCE = 0,/* image = (sqrt(running mean),1), kernels/raytrac
 enum { RT_MESH_FIRST_FRONT = 0, /* first front-facing face in order per mesh, kernels/raytracer.cl:291-303 */
        RT_MESH_NEAREST = 1 };   /* nearest front-facing face, ties -> lowest face (BVH-compatible rule) */
 enum { RT_ACCEL_AUTO = 0, RT_ACCEL_BRUTE = 1, RT_ACCEL_BVH = 2 };
+enum { RT_HEAD_ON = 0,        /* memoise the sample-independent head of every pixel's path */
+       RT_HEAD_OFF = 1 };     /* trace every segment of every sample, as the reference does */
 
 typedef struct rt_params {
     uint32_t max_depth;   /* reference: #define DEPTH 30 (kernels/raytracer.cl:5) */
@@ -57,11 +59,15 @@ typedef struct rt_params {
     uint32_t arith;       /* RT_ARITH_* */
     uint32_t mesh_mode;   /* RT_MESH_*  */
     uint32_t accel;       /* RT_ACCEL_* */
+    uint32_t path_head;   /* RT_HEAD_*  */
 } rt_params;
 
 typedef struct rt_stats {
-    uint64_t rays_total;      /* nearest-hit queries (path segments) since the last rt_render / rt_clear_accum */
+    uint64_t rays_total;      /* path segments (the reference's hitScene calls) since the last rt_render / rt_clear_accum */
     uint64_t rays_last;       /* ... of the last render call */
+    uint64_t queries_last;    /* nearest-hit queries the last render call actually executed on the device: equal to
+                                 rays_last with RT_HEAD_OFF; with RT_HEAD_ON the segments of a path head are traced
+                                 once per pixel (when the head is built) instead of once per sample */
     double   ms_last;         /* device time of the last render call (CUDA events on the context's stream) */
     uint32_t samples_done;    /* samples accumulated in the image / accumulation buffer */
     uint32_t kernel_launches; /* kernels launched by this context since creation */
@@ -102,6 +108,9 @@ int rt_render_again(rt_ctx* ctx, const float camera[12]);
  * ranges rendered on different GPUs can be summed). */
 int rt_render_samples(rt_ctx* ctx, const float camera[12], uint32_t first, uint32_t n_samples, uint32_t accum_mode);
 int rt_clear_accum(rt_ctx* ctx);
+/* Forget everything derived from (scene, camera): path heads and certified primary ids are rebuilt by the next
+ * render call.  The reference has no such state (it re-traces every segment of every sample). */
+int rt_invalidate_caches(rt_ctx* ctx);
 /* image = (sqrt(accum.rgb / spp), 1): the tail of kernels/raytracer.cl:509,531 applied to a summed buffer. */
 int rt_finalize(rt_ctx* ctx, uint32_t total_spp);
 

@@ -89,7 +89,7 @@ struct rt_ctx {
     BvhBuffers bvh;                   // GPU-built LBVH (empty while the brute-force path is active)
     size_t staged_bytes = 0;          // shared memory the brute-force path needs for this scene
     uint32_t n_finite = 0;            // spheres + lenses + triangles
-    rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO};
+    rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO, RT_HEAD_ON};
     uint32_t sample_counter = 0;
     int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
     // fast arithmetic: Exact primary-hit ids of the current (scene, camera, mesh rule), see ensure_certified()
@@ -97,6 +97,18 @@ struct rt_ctx {
     float certify_cam[12] = {0};
     uint32_t certify_mesh_mode = 0;
     bool certify_valid = false;
+    // path heads of the current (scene, camera, depth, mesh rule, accel), see ensure_head()
+    float4* d_head_rec = nullptr;
+    uint8_t* d_head_flag = nullptr;
+    uint32_t* d_head_list = nullptr;
+    uint32_t* d_head_count = nullptr;
+    void* d_head_scratch = nullptr;
+    size_t head_scratch_bytes = 0;
+    uint32_t head_n_slots = 0, head_n_stoch = 0;
+    uint64_t head_segments = 0;       // sum over the pixels of the segments in their path head
+    float head_cam[12] = {0};
+    uint32_t head_mesh_mode = 0, head_depth = 0;
+    bool head_bvh = false, head_valid = false;
     rt_stats stats{};
 };
 
@@ -272,6 +284,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     free_lbvh(c->bvh);
     c->max_texture_used = max_tex;
     c->certify_valid = false;
+    c->head_valid = false;
     c->have_scene = true;
     return RT_OK;
 }
@@ -285,7 +298,7 @@ int ensure_accel(rt_ctx* c) {
         return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu)", c->staged_bytes, kMaxStagedBytes);
     if (want_bvh && c->n_finite == 0) want_bvh = false;
     if (!want_bvh) {
-        if (c->bvh.n_leaves) { free_lbvh(c->bvh); c->stats.bvh_nodes = 0; c->certify_valid = false; }
+        if (c->bvh.n_leaves) { free_lbvh(c->bvh); c->stats.bvh_nodes = 0; c->certify_valid = false; c->head_valid = false; }
         return RT_OK;
     }
     if (c->sc.n_tri > 0 && c->prm.mesh_mode != RT_MESH_NEAREST)
@@ -299,6 +312,7 @@ int ensure_accel(rt_ctx* c) {
     c->stats.bvh_nodes = c->bvh.n_leaves > 1 ? c->bvh.n_leaves - 1 : 1;
     c->stats.kernel_launches += 8;
     c->certify_valid = false;
+    c->head_valid = false;
     return RT_OK;
 }
 DevBvh dev_bvh(const rt_ctx* c) {
@@ -325,6 +339,49 @@ int ensure_certified(rt_ctx* c, const float* cam) {
     std::memcpy(c->certify_cam, cam, 48);
     c->certify_mesh_mode = c->prm.mesh_mode;
     c->certify_valid = true;
+    return RT_OK;
+}
+
+// Path heads (rt_device.h, DevHead): one Exact walk per pixel up to its first random-consuming hit, then a
+// partition of the slots into stochastic / other.  Rebuilt only when scene, camera, depth, mesh rule or the
+// intersection path change.  *rebuilt tells the caller whether this call did the work.
+int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
+    *rebuilt = false;
+    const bool bvh = c->bvh.n_leaves != 0;
+    if (c->head_valid && c->head_mesh_mode == c->prm.mesh_mode && c->head_depth == c->prm.max_depth && c->head_bvh == bvh &&
+        std::memcmp(c->head_cam, cam, 48) == 0)
+        return RT_OK;
+    const uint32_t n_slots = (uint32_t)(((c->W + 7) / 8) * ((c->H + 3) / 4)) * 32u;
+    if (!c->d_head_rec) {
+        CU(cudaMalloc(&c->d_head_rec, (size_t)n_slots * 4 * sizeof(float4)));
+        CU(cudaMalloc(&c->d_head_flag, n_slots));
+        CU(cudaMalloc(&c->d_head_list, (size_t)n_slots * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->d_head_count, sizeof(uint32_t)));
+        size_t bytes = 0;
+        CU(partition_heads(c->d_head_flag, n_slots, c->d_head_list, c->d_head_count, nullptr, bytes, c->stream));
+        CU(cudaMalloc(&c->d_head_scratch, bytes ? bytes : 1));
+        c->head_scratch_bytes = bytes;
+    }
+    HeadLaunch L{};
+    L.sc = c->sc;
+    std::memcpy(L.cam, cam, 48);
+    L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth; L.mesh_mode = c->prm.mesh_mode; L.bvh = dev_bvh(c);
+    L.rec = c->d_head_rec; L.flag = c->d_head_flag; L.n_slots = n_slots; L.segments = c->d_rays + 2;
+    CU(cudaMemsetAsync(c->d_rays + 2, 0, sizeof(unsigned long long), c->stream));
+    CU(launch_head(L, c->stream));
+    size_t bytes = c->head_scratch_bytes;
+    CU(partition_heads(c->d_head_flag, n_slots, c->d_head_list, c->d_head_count, c->d_head_scratch, bytes, c->stream));
+    uint32_t n_stoch = 0;
+    unsigned long long seg = 0;
+    CU(cudaMemcpyAsync(&n_stoch, c->d_head_count, sizeof n_stoch, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(&seg, c->d_rays + 2, sizeof seg, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->head_n_slots = n_slots; c->head_n_stoch = n_stoch; c->head_segments = seg;
+    std::memcpy(c->head_cam, cam, 48);
+    c->head_mesh_mode = c->prm.mesh_mode; c->head_depth = c->prm.max_depth; c->head_bvh = bvh;
+    c->head_valid = true;
+    c->stats.kernel_launches += 3;   // k_head + CUB's partition (init + sweep)
+    *rebuilt = true;
     return RT_OK;
 }
 
@@ -363,7 +420,7 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaMalloc(&c->d_image, px * sizeof(float4))) != cudaSuccess) return bail(e, "image buffer");
     if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4))) != cudaSuccess) return bail(e, "accumulation buffer");
-    if ((e = cudaMalloc(&c->d_rays, sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counter");
+    if ((e = cudaMalloc(&c->d_rays, 4 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counters");   // rays, queries, head segments
     c->d_accum = c->d_accum_own;
     cudaMemsetAsync(c->d_image, 0, px * sizeof(float4), c->stream);
     cudaMemsetAsync(c->d_accum, 0, px * sizeof(float4), c->stream);
@@ -382,6 +439,7 @@ int rt_destroy(rt_ctx* c) {
         Guard g(c);
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
         cudaFree(c->d_certify);
+        cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
         c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
@@ -454,7 +512,7 @@ int rt_set_random_table(rt_ctx* c, const float* table, uint32_t n_floats) {
 int rt_set_params(rt_ctx* c, const rt_params* p) {
     if (!c || !p) return fail(RT_ERR_INVALID, "rt_set_params: null argument");
     if (p->max_depth == 0) return fail(RT_ERR_INVALID, "max_depth must be >= 1");
-    if (p->rng_mode > 1 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
+    if (p->rng_mode > 1 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2 || p->path_head > 1) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
     c->prm = *p;
     return RT_OK;
 }
@@ -483,22 +541,38 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
-    if (c->prm.arith == RT_ARITH_FAST) {
+    L.queries = c->d_rays + 1;
+    // Path heads: brute-force scenes (the LBVH kernels still trace every segment of every sample).
+    const bool use_head = c->prm.path_head == RT_HEAD_ON && c->bvh.n_leaves == 0;
+    if (!use_head && c->prm.arith == RT_ARITH_FAST) {
         int r = ensure_certified(c, cam);
         if (r != RT_OK) return r;
         L.certify_id = c->d_certify;
     }
-    CU(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_rays, 0, 2 * sizeof(unsigned long long), c->stream));
     CU(cudaEventRecord(c->ev0, c->stream));
-    CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
+    bool head_rebuilt = false;
+    if (use_head) {
+        int r = ensure_head(c, cam, &head_rebuilt);      // inside the timed region of this call
+        if (r != RT_OK) return r;
+        L.head.rec = c->d_head_rec; L.head.flag = c->d_head_flag; L.head.list = c->d_head_list;
+        L.head.n_slots = c->head_n_slots; L.head.n_stoch = c->head_n_stoch;
+        CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_tail_strict(L, c->stream) : launch_trace_tail_fast(L, c->stream));
+    } else {
+        CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
+    }
     CU(cudaEventRecord(c->ev1, c->stream));
-    unsigned long long rays = 0;
-    CU(cudaMemcpyAsync(&rays, c->d_rays, sizeof rays, cudaMemcpyDeviceToHost, c->stream));
+    unsigned long long counters[2] = {0, 0};
+    CU(cudaMemcpyAsync(counters, c->d_rays, sizeof counters, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     float ms = 0.0f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    // rays = path segments, what the reference's hitScene is called for: with path heads every sample of a pixel
+    // owns the segments of the head although they were traced once.
+    const unsigned long long rays = use_head ? (unsigned long long)n * c->head_segments + counters[1] : counters[0];
     c->stats.ms_last = ms;
     c->stats.rays_last = rays;
+    c->stats.queries_last = use_head ? counters[1] + (head_rebuilt ? c->head_segments : 0ull) : counters[0];
     c->stats.rays_total += rays;
     c->stats.kernel_launches += 1;
     return RT_OK;
@@ -534,6 +608,12 @@ int rt_clear_accum(rt_ctx* c) {
     CU(cudaMemsetAsync(c->d_accum, 0, (size_t)c->W * c->H * sizeof(float4), c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->stats.samples_done = 0; c->stats.rays_total = 0;
+    return RT_OK;
+}
+int rt_invalidate_caches(rt_ctx* c) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    c->head_valid = false;
+    c->certify_valid = false;
     return RT_OK;
 }
 int rt_finalize(rt_ctx* c, uint32_t spp) {

@@ -54,6 +54,25 @@ struct DevTexture {
     int w, h, layers;
 };
 
+// Path heads.  The reference shoots the SAME primary ray for every sample of a pixel (no jitter,
+// kernels/raytracer.cl:500-505,517-522), and mirrors, refractive surfaces, lights and misses consume no random
+// numbers (kernels/raytracer.cl:454-479), so the path of a pixel is identical for all samples up to its first hit on
+// a diffuse / textured / dielectric surface.  That head is computed once per (scene, camera) by k_head_* in Exact
+// arithmetic; the render kernels restart every sample from the stored state.
+// Slots are pixel tiles in launch order: slot = tile * 32 + lane, tile = 8 x 4 pixels.
+//   rec[0 * n_slots + s] = (o.xyz, hit t)     rec[1 * n_slots + s] = (d.xyz, hit bu)
+//   rec[2 * n_slots + s] = (out.rgb, hit bv)  rec[3 * n_slots + s] = (bounce index, hit id, hit aux, material id) as bits
+//   flag[s]: 0 outside the frame, 1 terminal (rec[2].rgb is the colour of every sample, rec[3].x the segment count),
+//            2 stochastic (restart state of the first random-consuming hit).
+// list[0, n_stoch) = stochastic slots in slot order; list[n_slots - n_rest, n_slots) = all other slots (reversed).
+struct DevHead {
+    const float4* rec;
+    const uint8_t* flag;
+    const uint32_t* list;
+    uint32_t n_slots, n_stoch;
+};
+constexpr uint8_t kHeadDead = 0, kHeadTerminal = 1, kHeadStochastic = 2;
+
 struct TraceLaunch {
     DevScene sc;
     DevTexture tex;
@@ -68,6 +87,21 @@ struct TraceLaunch {
     const uint32_t* certify_id; // fast arithmetic: Exact primary-hit id per pixel (nullptr = no certification)
     DevBvh bvh;                // n_leaves == 0: brute-force path over the staged scene
     uint32_t bvh_regen;        // LBVH kernel: waiting lanes that trigger a shading/regeneration phase (0 = default 8)
+    DevHead head;              // path heads of the frame (k_trace_tail_* only)
+    unsigned long long* queries; // device counter: nearest-hit queries executed (k_trace_tail_*)
+};
+
+// k_head_*: the sample-independent head of every pixel's path (see rt_kernels.cuh, "path heads").
+struct HeadLaunch {
+    DevScene sc;
+    float cam[12];
+    int W, H;
+    uint32_t depth, mesh_mode;
+    DevBvh bvh;
+    float4* rec;               // 4 x n_slots
+    uint8_t* flag;             // n_slots
+    uint32_t n_slots;
+    unsigned long long* segments;   // device counters: [0] sum of head segments over the live pixels
 };
 
 struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays
@@ -103,6 +137,11 @@ cudaError_t launch_probe_hits_strict(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_bounce_strict(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s);
+cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s);                 // Exact arithmetic, both arms
+cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s);
+cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s);
+// list = slots partitioned by flag == kHeadStochastic (CUB DevicePartition); *n_stoch on the device
+cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s);
 cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);
 cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t s);
 

@@ -481,38 +481,44 @@ __device__ __forceinline__ V3 reflect_dir(V3 d, V3 n) {            // cl:362-365
     return A::normalize(vsub<A>(d, vscale<A>(n, k)));
 }
 
+// Material of the winning primitive (cl:162, 189, 250, 314).
+__device__ __forceinline__ uint32_t hit_material(const DevScene& sc, const float4* __restrict__ S, const Hit& h) {
+    const uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
+    if (kind == kKindSphere) return __ldg(sc.sph_mat + idx);
+    if (kind == kKindPlane) return __ldg(sc.pla_mat + idx);
+    if (kind == kKindLens) return __ldg(sc.len_mat + idx);
+    const uint4* M = reinterpret_cast<const uint4*>(S + sc.stream_f4);
+    return M[3 * __ldg(sc.tri_mesh + h.aux)].w;
+}
+
 // Hit-point data for the winning primitive (cl:158-161, 185-188, 246-249, 281-285, 296, 314) followed by one
 // iteration of getCol's switch (cl:454-479).  Returns true when the path ends (light).
 template <class A>
-__device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restrict__ S, const Hit& h, const PixelRng& pr,
+__device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restrict__ S, const Hit& h, uint32_t mat_id, const PixelRng& pr,
                                       V3& o, V3& d, V3& out, uint32_t sample, uint32_t bounce) {
     const DevScene& sc = *env.sc;
     const uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
     const V3 p = vmad<A>(d, h.t, o);                                // cl:141-143
     V3 n;
-    uint32_t mat_id, tex_id = 0u;
+    uint32_t tex_id = 0u;
     float uvx = 0.0f, uvy = 0.0f;
     if (kind == kKindSphere) {
         const float4 s = __ldg(sc.sph_shade + idx);
         n = A::vdiv(vsub<A>(p, mk(s.x, s.y, s.z)), s.w);
-        mat_id = __ldg(sc.sph_mat + idx);
     } else if (kind == kKindPlane) {
         const float4 pn = __ldg(sc.pla_normal + idx);
         const V3 nn = mk(pn.x, pn.y, pn.z);
         const float a = dot<A>(d, nn);
         const float sg = (a != a) ? 0.0f : (a > 0.0f ? 1.0f : (a < 0.0f ? -1.0f : a));
         n = vscale<A>(neg(nn), sg);                                 // cl:187
-        mat_id = __ldg(sc.pla_mat + idx);
     } else if (kind == kKindLens) {
         const float4 l = __ldg(sc.len_shade + 2 * idx + h.aux);
         n = A::vdiv(vsub<A>(p, mk(l.x, l.y, l.z)), l.w);
-        mat_id = __ldg(sc.len_mat + idx);
     } else {
         const float4 q2 = S[sc.off_tri + 3 * h.aux + 2];
         n = mk(q2.y, q2.z, q2.w);
         const uint32_t mesh = __ldg(sc.tri_mesh + h.aux);
         const uint4* M = reinterpret_cast<const uint4*>(S + sc.stream_f4);
-        mat_id = M[3 * mesh].w;
         tex_id = M[3 * mesh + 1].x;
         const float2 ua = __ldg(sc.tri_uv + 3 * h.aux), ub = __ldg(sc.tri_uv + 3 * h.aux + 1), uc = __ldg(sc.tri_uv + 3 * h.aux + 2);
         const float w = A::sub(A::sub(1.0f, h.bu), h.bv);           // cl:101-103
@@ -631,7 +637,7 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
             ++rays;
             bool ended;
             if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }   // cl:450-452
-            else ended = shade<A>(env, S, h, pr, o, d, out, k, i);
+            else ended = shade<A>(env, S, h, hit_material(p.sc, S, h), pr, o, d, out, k, i);
             ++i;
             if (ended || i >= p.depth) {
                 if (p.accum_mode == 1u) {                   // linear sum (what the sample split reduces)
@@ -730,7 +736,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
             ++rays;
             bool ended;
             if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }
-            else ended = shade<A>(env, S, h, pr, o, d, out, k, i);
+            else ended = shade<A>(env, S, h, hit_material(p.sc, S, h), pr, o, d, out, k, i);
             ++i;
             if (ended || i >= p.depth) {
                 if (p.accum_mode == 1u) {
@@ -752,6 +758,169 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
     if (live) *px = acc;
     for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(RT_FULL, rays, off);
     if (lane == 0 && rays) atomicAdd(p.rays, rays);
+}
+
+// ------------------------------------------------------------------------------------------------ path heads
+// See DevHead (rt_device.h): the head of a pixel's path — everything up to its first hit on a surface whose
+// material draws random numbers — is the same for every sample, because the reference shoots the same primary ray
+// for each sample (cl:500-505, 517-522) and mirrors / refractive surfaces / lights / misses are deterministic
+// (cl:454-479).  k_head_* walks it once per pixel, always in Exact arithmetic (so the primary hits of the fast arm
+// are the reference's by construction); k_trace_tail_* restarts every sample from the stored state.
+
+// One sample's radiance into the accumulator: linear sum, or the reference's sqrt(mean) chain (cl:509, 524-531).
+template <class A>
+__device__ __forceinline__ void accumulate_sample(float4& acc, V3 out, uint32_t k, uint32_t accum_mode) {
+    if (accum_mode == 1u) {
+        acc.x = A::add(acc.x, out.x); acc.y = A::add(acc.y, out.y); acc.z = A::add(acc.z, out.z); acc.w += 1.0f;
+    } else if (k == 0u) {
+        acc = make_float4(A::sqrt(out.x), A::sqrt(out.y), A::sqrt(out.z), 1.0f);
+    } else {
+        const float a = A::div((float)k, (float)(k + 1u));
+        const float pr_ = A::mul(acc.x, acc.x), pg_ = A::mul(acc.y, acc.y), pb_ = A::mul(acc.z, acc.z);
+        acc = make_float4(A::sqrt(A::mad(A::sub(pr_, out.x), a, out.x)), A::sqrt(A::mad(A::sub(pg_, out.y), a, out.y)),
+                          A::sqrt(A::mad(A::sub(pb_, out.z), a, out.z)), 1.0f);
+    }
+}
+__device__ __forceinline__ void slot_pixel(uint32_t slot, int W, int& x, int& y) {
+    const int tiles_x = (W + 7) >> 3;
+    const int tile = (int)(slot >> 5), lane = (int)(slot & 31u);
+    x = (tile % tiles_x) * 8 + (lane & 7);
+    y = (tile / tiles_x) * 4 + (lane >> 3);
+}
+
+template <bool BVH>
+__device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
+    const float4* S = p.sc.stream;
+    if (!BVH) { stage_scene(p.sc, smem); S = smem; }
+    const uint32_t slot = blockIdx.x * kTraceThreads + threadIdx.x;
+    int x, y;
+    slot_pixel(slot, p.W, x, y);
+    const bool live = slot < p.n_slots && x < p.W && y < p.H;
+    unsigned long long seg = 0ull;
+    if (live) {
+        V3 o = mk(p.cam[0], p.cam[1], p.cam[2]), d = primary_dir<Exact>(p.cam, x, y, p.W, p.H), out = mk(1.0f, 1.0f, 1.0f);
+        uint32_t i = 0u, mat_id = 0u;
+        uint8_t flag = kHeadTerminal;
+        Hit h;
+        ShadeEnv env; env.sc = &p.sc; env.tex = nullptr; env.table = nullptr; env.rng_mode = 0u;
+        PixelRng pr; pr.vec_base = pr.uni_base = pr.hp = 0u;
+        for (;;) {
+            if (BVH) nearest_hit_bvh<Exact>(p.sc, S, p.bvh, o, d, h);
+            else nearest_hit_lane<Exact>(p.sc, S, o, d, p.mesh_mode, h);
+            ++seg;
+            if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); break; }                       // cl:450-452
+            mat_id = hit_material(p.sc, S, h);
+            const int type = __float_as_int(__ldg(p.sc.mat + 2 * mat_id).x);
+            if (type == 5) { const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1); out = vmin(out, mk(m1.x, m1.y, m1.z)); break; }   // cl:459-462
+            if (type == 2 || type == 3 || type == 4) { flag = kHeadStochastic; break; }       // draws random numbers
+            shade<Exact>(env, S, h, mat_id, pr, o, d, out, 0u, i);                             // mirror / refractive
+            if (++i >= p.depth) break;                                                          // cl:447: loop exhausted
+        }
+        if (flag == kHeadStochastic) {
+            p.rec[slot] = make_float4(o.x, o.y, o.z, h.t);
+            p.rec[p.n_slots + slot] = make_float4(d.x, d.y, d.z, h.bu);
+            p.rec[2u * p.n_slots + slot] = make_float4(out.x, out.y, out.z, h.bv);
+            p.rec[3u * p.n_slots + slot] = make_float4(__uint_as_float(i), __uint_as_float(h.id), __uint_as_float(h.aux), __uint_as_float(mat_id));
+        } else {
+            p.rec[2u * p.n_slots + slot] = make_float4(out.x, out.y, out.z, 0.0f);
+        }
+        p.flag[slot] = flag;
+    } else if (slot < p.n_slots) {
+        p.flag[slot] = kHeadDead;
+    }
+    seg = __reduce_add_sync(RT_FULL, (unsigned)seg);
+    if ((threadIdx.x & 31) == 0 && seg) atomicAdd(p.segments, seg);
+}
+
+// Pixels whose whole path is deterministic: every sample has the colour stored by k_head.
+template <class A>
+__device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) {
+    if (j >= p.head.n_slots - p.head.n_stoch) return;
+    const uint32_t slot = __ldg(p.head.list + (p.head.n_slots - 1u - j));
+    if (__ldg(p.head.flag + slot) != kHeadTerminal) return;
+    int x, y;
+    slot_pixel(slot, p.W, x, y);
+    const float4 r2 = __ldg(p.head.rec + 2u * p.head.n_slots + slot);
+    const V3 out = mk(r2.x, r2.y, r2.z);
+    float4* px = p.target + (size_t)y * p.W + x;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (p.accum_mode == 1u || p.first > 0u) acc = *px;
+    const bool black = out.x == 0.0f && out.y == 0.0f && out.z == 0.0f;
+    if (black && p.accum_mode == 1u && acc.w == floorf(acc.w) && acc.w >= 0.0f && acc.w + (float)p.n <= 16777216.0f) {
+        acc.w += (float)p.n;                                   // n exact additions of 1.0f; x + 0.0f == x
+    } else if (black && p.accum_mode == 0u && acc.x == 0.0f && acc.y == 0.0f && acc.z == 0.0f) {
+        acc = make_float4(0.0f, 0.0f, 0.0f, 1.0f);             // the sqrt(mean) chain of zeros stays zero
+    } else {
+        for (uint32_t k = p.first; k < p.first + p.n; ++k) accumulate_sample<A>(acc, out, k, p.accum_mode);
+    }
+    *px = acc;
+}
+
+// trace + retrace + getCol for samples [first, first+n) of the stochastic pixels, restarting from the path heads.
+// Every lane entering a trip holds a pending hit on a surface that is neither a miss nor a light: the trip shades it,
+// traces the bounced ray, and closes the path on a miss (cl:450-452), a light (cl:459-462) or at the depth limit.  So
+// every live lane does exactly one nearest-hit query per trip; a finished path restarts from the stored head in place.
+template <class A>
+__device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* smem) {
+    const uint32_t stoch_blocks = (p.head.n_stoch + kTraceThreads - 1u) / kTraceThreads;
+    if (blockIdx.x >= stoch_blocks) { terminal_body<A>(p, (blockIdx.x - stoch_blocks) * kTraceThreads + threadIdx.x); return; }
+    stage_scene(p.sc, smem);
+    const float4* S = smem;
+    uint8_t* list = warp_list(p.sc, smem);
+    float4* hs = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(smem + p.sc.stream_f4 + 3u * p.sc.n_mesh + pd_f4(p.sc)) +
+                                           (kTraceThreads / 32) * 1024u) + threadIdx.x;   // [4][kTraceThreads] restart state
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t j = blockIdx.x * kTraceThreads + threadIdx.x;
+    const bool live = j < p.head.n_stoch;
+    const uint32_t slot = live ? __ldg(p.head.list + j) : 0u;
+    int x, y;
+    slot_pixel(slot, p.W, x, y);
+#pragma unroll
+    for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
+
+    const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
+    ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
+    float4* px = p.target + (size_t)y * p.W + x;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (live && (p.accum_mode == 1u || p.first > 0u)) acc = *px;
+    const uint32_t k_end = p.first + p.n;
+    uint32_t k = live ? p.first : k_end, i, mat_id;
+    V3 o, d, out;
+    Hit h;
+    auto restart = [&]() {
+        const float4 r0 = hs[0], r1 = hs[kTraceThreads], r2 = hs[2 * kTraceThreads], r3 = hs[3 * kTraceThreads];
+        o = mk(r0.x, r0.y, r0.z); d = mk(r1.x, r1.y, r1.z); out = mk(r2.x, r2.y, r2.z);
+        h.t = r0.w; h.bu = r1.w; h.bv = r2.w;
+        i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
+    };
+    restart();
+    uint32_t queries = 0u;
+
+    while (__any_sync(RT_FULL, k < k_end)) {
+        const bool active = k < k_end;
+        if (active) { shade<A>(env, S, h, mat_id, pr, o, d, out, k, i); ++i; }
+        const bool q = active && i < p.depth;
+        nearest_hit_warp<A>(p.sc, S, list, o, d, q, p.mesh_mode, h);
+        if (active) {
+            bool ended = !q;                                                        // cl:447: depth exhausted, keep out
+            if (q) {
+                ++queries;
+                if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }  // cl:450-452
+                else {
+                    mat_id = hit_material(p.sc, S, h);
+                    if (__float_as_int(__ldg(p.sc.mat + 2 * mat_id).x) == 5) {      // light, cl:459-462
+                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                        out = vmin(out, mk(m1.x, m1.y, m1.z));
+                        ended = true;
+                    }
+                }
+            }
+            if (ended) { accumulate_sample<A>(acc, out, k, p.accum_mode); ++k; restart(); }
+        }
+    }
+    if (live) *px = acc;
+    queries = __reduce_add_sync(RT_FULL, queries);                                   // < 2^32 per warp launch
+    if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
 }
 
 // Nearest hit of arbitrary rays (rays6 != nullptr) or of the primary rays of the frame; same code path as the
@@ -806,7 +975,7 @@ __device__ __forceinline__ void probe_bounce_body(const ProbeLaunch& p, float4* 
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
     bool ended;
     if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }
-    else ended = shade<A>(env, smem, h, pr, o, d, out, p.sample[i], p.bounce[i]);
+    else ended = shade<A>(env, smem, h, hit_material(p.sc, smem, h), pr, o, d, out, p.sample[i], p.bounce[i]);
     p.rays6_out[6 * i] = o.x; p.rays6_out[6 * i + 1] = o.y; p.rays6_out[6 * i + 2] = o.z;
     p.rays6_out[6 * i + 3] = d.x; p.rays6_out[6 * i + 4] = d.y; p.rays6_out[6 * i + 5] = d.z;
     p.col3[3 * i] = out.x; p.col3[3 * i + 1] = out.y; p.col3[3 * i + 2] = out.z;
@@ -817,9 +986,16 @@ inline size_t staged_bytes(const DevScene& sc) {
     return ((size_t)sc.stream_f4 + 3u * sc.n_mesh + ((sc.n_tri + 3u) >> 2)) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
 }
 
+// grid of k_trace_tail_*: blocks of stochastic slots, then blocks over the rest of the list (terminal pixels)
+inline size_t tail_work_items(const TraceLaunch& p) {
+    const size_t T = kTraceThreads;
+    return ((p.head.n_stoch + T - 1) / T + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
+}
+constexpr size_t kHeadStateBytes = 4u * kTraceThreads * sizeof(float4);   // restart state of k_trace_tail_*
+
 template <class K, class P>
-inline cudaError_t launch_staged(K kernel, const P& p, size_t work_items, cudaStream_t s, bool bvh = false) {
-    const size_t smem = bvh ? 0 : staged_bytes(p.sc);
+inline cudaError_t launch_staged(K kernel, const P& p, size_t work_items, cudaStream_t s, bool bvh = false, size_t extra = 0) {
+    const size_t smem = bvh ? 0 : staged_bytes(p.sc) + extra;
     if (smem > kMaxStagedBytes) return cudaErrorInvalidValue;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -2,6 +2,9 @@
 // FP32-issue microbenchmark that supplies the roofline denominator MEASURED_PEAKS.json lacks.
 #include "rt_device.h"
 
+#include <cub/cub.cuh>
+#include <thrust/iterator/counting_iterator.h>
+
 namespace rtb {
 
 __global__ void k_finalize(const float4* __restrict__ accum, float4* __restrict__ image, int n, float inv_spp) {
@@ -15,6 +18,16 @@ cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, ui
     if (n_pixels <= 0) return cudaSuccess;
     k_finalize<<<(n_pixels + 255) / 256, 256, 0, s>>>(accum, image, n_pixels, 1.0f / (float)spp);
     return cudaGetLastError();
+}
+
+// Slots with a stochastic path head to the front of `list` (in slot order), all others to the back (reversed).
+struct IsStochastic {
+    const uint8_t* flag;
+    __device__ bool operator()(uint32_t slot) const { return flag[slot] == kHeadStochastic; }
+};
+cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s) {
+    thrust::counting_iterator<uint32_t> slots(0u);
+    return cub::DevicePartition::If(scratch, scratch_bytes, slots, list, d_n_stoch, (int)n_slots, IsStochastic{flag}, s);
 }
 
 // 16 independent FFMA chains per thread; 2 flops / 1 issue slot per FFMA per lane.

@@ -19,6 +19,7 @@ ARITH_STRICT, ARITH_FAST = 0, 1
 ACCUM_REFERENCE, ACCUM_SUM = 0, 1
 MESH_FIRST_FRONT, MESH_NEAREST = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_BVH = 0, 1, 2
+HEAD_ON, HEAD_OFF = 0, 1
 ID_MISS = 0xFFFFFFFF
 TABLE_FLOATS = 400000
 
@@ -39,11 +40,11 @@ class SceneDesc(C.Structure):
 
 class Params(C.Structure):
     _fields_ = [("max_depth", C.c_uint32), ("rng_mode", C.c_uint32), ("seed", C.c_uint32), ("arith", C.c_uint32),
-                ("mesh_mode", C.c_uint32), ("accel", C.c_uint32)]
+                ("mesh_mode", C.c_uint32), ("accel", C.c_uint32), ("path_head", C.c_uint32)]
 
 
 class Stats(C.Structure):
-    _fields_ = [("rays_total", C.c_uint64), ("rays_last", C.c_uint64), ("ms_last", C.c_double),
+    _fields_ = [("rays_total", C.c_uint64), ("rays_last", C.c_uint64), ("queries_last", C.c_uint64), ("ms_last", C.c_double),
                 ("samples_done", C.c_uint32), ("kernel_launches", C.c_uint32), ("n_primitives", C.c_uint32),
                 ("bvh_nodes", C.c_uint32)]
 
@@ -68,7 +69,7 @@ def lib():
         "rt_make_random_table": [u32, vp], "rt_set_random_table": [vp, vp, u32],
         "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
         "rt_render": [vp, vp], "rt_render_again": [vp, vp], "rt_render_samples": [vp, vp, u32, u32, u32],
-        "rt_clear_accum": [vp], "rt_finalize": [vp, u32], "rt_read_image": [vp, vp], "rt_read_accum": [vp, vp],
+        "rt_clear_accum": [vp], "rt_invalidate_caches": [vp], "rt_finalize": [vp, u32], "rt_read_image": [vp, vp], "rt_read_accum": [vp, vp],
         "rt_read_primary_ids": [vp, vp, vp, vp], "rt_get_stats": [vp, C.POINTER(Stats)],
         "rt_accum_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_image_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
@@ -203,8 +204,8 @@ class Context:
         _check(self.L.rt_set_random_table(self.h, t.ctypes.data, t.size))
 
     def set_params(self, max_depth=30, rng_mode=RNG_TABLE, seed=0, arith=ARITH_STRICT, mesh_mode=MESH_FIRST_FRONT,
-                   accel=ACCEL_AUTO):
-        p = Params(max_depth, rng_mode, seed, arith, mesh_mode, accel)
+                   accel=ACCEL_AUTO, path_head=HEAD_ON):
+        p = Params(max_depth, rng_mode, seed, arith, mesh_mode, accel, path_head)
         _check(self.L.rt_set_params(self.h, C.byref(p)))
 
     @staticmethod
@@ -227,6 +228,9 @@ class Context:
 
     def clear_accum(self):
         _check(self.L.rt_clear_accum(self.h))
+
+    def invalidate_caches(self):
+        _check(self.L.rt_invalidate_caches(self.h))
 
     def finalize(self, spp):
         _check(self.L.rt_finalize(self.h, spp))

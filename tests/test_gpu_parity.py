@@ -243,3 +243,36 @@ def test_errors_are_reported_not_fatal(rt, scenes, table):
     with pytest.raises(rt.RtError):
         ctx.render(fx.camera(60, 1.0))               # table mode without a table
     ctx.close()
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+@pytest.mark.parametrize("name,W,H,depth", [("default", 640, 360, 30), ("c3", 480, 270, 30), ("default", 203, 131, 3)])
+def test_path_heads_change_nothing(rt, scenes, table, name, W, H, depth, arith):
+    """Memoising the sample-independent head of every path (RT_HEAD_ON) must not change one bit of the strict image,
+    nor the number of path segments; the executed queries drop.  Fast arm: same statistics (the head is walked in
+    Exact arithmetic there, so single pixels may differ from the all-Fused path)."""
+    from rtb200 import fixtures as fx
+    cam = fx.camera(60, W / H)
+    A = rt.ARITH_STRICT if arith == "strict" else rt.ARITH_FAST
+    out = {}
+    for mode in (rt.HEAD_OFF, rt.HEAD_ON):
+        with make_ctx(rt, scenes, name, W, H, table, max_depth=depth, arith=A, rng_mode=rt.RNG_COUNTER, seed=7, path_head=mode) as ctx:
+            ctx.render_samples(cam, 0, 6, rt.ACCUM_REFERENCE)
+            img = ctx.read_image().copy()
+            st = ctx.stats()
+            rays, queries = st.rays_last, st.queries_last
+            ctx.clear_accum()
+            ctx.render_samples(cam, 3, 5, rt.ACCUM_SUM)      # heads cached: no head queries in this call
+            acc = ctx.read_accum().copy()
+            out[mode] = (img, rays, queries, acc, ctx.stats().rays_last, ctx.stats().queries_last)
+    off, on = out[rt.HEAD_OFF], out[rt.HEAD_ON]
+    assert off[1] == off[2] and off[4] == off[5]            # without heads every segment is a query
+    assert on[2] < on[1] and on[5] < on[4]
+    if arith == "strict":
+        assert np.array_equal(bits(on[0]), bits(off[0]))
+        assert np.array_equal(bits(on[3]), bits(off[3]))
+        assert on[1] == off[1] and on[4] == off[4]
+    else:
+        assert abs(float((on[0][..., :3] ** 2).mean()) - float((off[0][..., :3] ** 2).mean())) < 5e-3
+        assert abs(on[1] - off[1]) <= 1e-3 * off[1]
+        assert np.all(on[3][..., 3] == 5.0) and np.all(off[3][..., 3] == 5.0)

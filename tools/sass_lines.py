@@ -8,7 +8,7 @@ hdr = rows[1]; data = [r for r in rows[2:] if len(r) > 10]
 iS, iE, iT = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 # disassembly: find .text.<kernel> section
 lines = open(dis).read().split("\n")
-start = [i for i, l in enumerate(lines) if l.strip().startswith(".section") and (".text." + kernel) in l][0]
+start = [i for i, l in enumerate(lines) if l.strip().startswith(".section") and (".text." + kernel + ",") in l][0]
 cur = None; ins = []
 for l in lines[start + 1:]:
     if l.strip().startswith(".section"): break
