@@ -39,8 +39,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--spp", type=int, default=None)
     ap.add_argument("--arith", default="fast", choices=["fast", "strict"])
-    ap.add_argument("--rng", default="counter", choices=["counter", "table"])
+    ap.add_argument("--rng", default="counter_table", choices=["counter_table", "counter", "table"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-heads", action="store_true", help="RT_HEAD_OFF: trace every segment of every sample (A/B of the path-head memoisation)")
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"],
                     help="BASELINE.json configs; the driver's default (and the headline) is c2")
     return ap.parse_args()
@@ -194,11 +195,12 @@ def main_b200(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     arith = rtb200.ARITH_FAST if a.arith == "fast" else rtb200.ARITH_STRICT
-    rng = rtb200.RNG_COUNTER if a.rng == "counter" else rtb200.RNG_TABLE
+    rng = {"counter": rtb200.RNG_COUNTER, "table": rtb200.RNG_TABLE, "counter_table": rtb200.RNG_COUNTER_TABLE}[a.rng]
 
     arr, tex, cam, table = load_inputs()
     ctx = rtb200.Context(W, H, local)
-    ctx.set_params(max_depth=DEPTH, rng_mode=rng, seed=1, arith=arith, mesh_mode=MESH_MODE)
+    ctx.set_params(max_depth=DEPTH, rng_mode=rng, seed=1, arith=arith, mesh_mode=MESH_MODE,
+                   path_head=rtb200.HEAD_OFF if a.no_heads else rtb200.HEAD_ON)
     ctx.upload_textures(tex); ctx.upload_scene(arr); ctx.set_random_table(table)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
@@ -211,11 +213,15 @@ def main_b200(a):
 
     peak_gslots, nominal_mhz = rtb200.measure_fp32_peak(local)
 
+    queries_steps = []
+
     def step():
         accum.zero_()
+        ctx.invalidate_caches()          # every step rebuilds the path heads: nothing is carried over between steps
         ctx.render_samples(cam, first, n_mine, rtb200.ACCUM_SUM)
-        rays = ctx.stats().rays_last
-        kms = ctx.stats().ms_last
+        st = ctx.stats()
+        rays, kms = st.rays_last, st.ms_trace_last
+        queries_steps.append(st.queries_last)
         reduce_to_rank0(accum)
         if rank == 0:
             ctx.finalize(spp)
@@ -296,6 +302,10 @@ def main_b200(a):
         k_ms = sum(kernel_ms) / len(kernel_ms)
         rays_launch = rays_steps[0]
         achieved = (SLOTS_PER_RAY or 0.0) * rays_launch / (k_ms * 1e-3) / 1e9
+        queries_launch = queries_steps[-1]
+        executed = (SLOTS_PER_RAY or 0.0) * queries_launch / (k_ms * 1e-3) / 1e9
+        bvh = int(ctx.stats().bvh_nodes) > 0
+        kernel = ("k_trace_%s_bvh" if bvh else ("k_trace_%s" if a.no_heads else "k_trace_tail_%s")) % a.arith
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_bytes = 2.0 * W * H * 16          # accumulation buffer read + write, once per launch
         out = {
@@ -305,7 +315,11 @@ def main_b200(a):
             "config": {"workload": WORKLOAD, "spp_total": spp, "spp_per_gpu": n_mine, "arith": a.arith, "rng": a.rng,
                        "parallelism": "spp-split x%d + 1 NCCL reduce" % world if world > 1 else "single GPU",
                        "l2": "flushed between steps (256 MiB memset); inputs are < 40 MB, the kernel is issue bound",
-                       "rays_per_step": int(rays_total / a.steps)},
+                       "rays_per_step": int(rays_total / a.steps),
+                       "ray": "one path segment = one hitScene call of the reference (kernels/raytracer.cl:322-360); the image is the "
+                              "reference's, sample for sample",
+                       "path_heads": (not a.no_heads) and not bvh,
+                       "queries_executed_per_step_rank0": int(queries_launch)},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
@@ -314,7 +328,12 @@ def main_b200(a):
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32_issue", "achieved": round(achieved, 1), "peak": round(peak_gslots, 1),
                          "unit": "G lane-slots/s", "frac": round(achieved / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
-                         "traffic": None, "kernel": "k_trace_%s" % a.arith, "kernel_ms": round(k_ms, 3),
+                         "traffic": None, "kernel": kernel, "kernel_ms": round(k_ms, 3),
+                         "achieved_executed": round(executed, 1),
+                         "frac_executed": round(executed / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
+                         "note": "achieved = 867 slots x path segments of the launch (the reference algorithm's work for this image) / "
+                                 "kernel time; achieved_executed counts only the nearest-hit queries the kernel ran: the head of a "
+                                 "path (same for every sample of a pixel) is traced once per pixel, not once per sample, so frac can exceed 1",
                          "slots_per_ray": SLOTS_PER_RAY, "rays_per_launch": int(rays_launch),
                          "peak_source": "measured live: dependent-free FFMA loop on all SMs (rt_measure_fp32_peak); "
                                         "MEASURED_PEAKS.json has no FP32 entry",
@@ -323,9 +342,9 @@ def main_b200(a):
         }
         out["config"]["bvh_nodes"] = int(ctx.stats().bvh_nodes)
         if world == 1 and not a.no_cpu_baseline and CONFIG in ("c1", "c2", "c3"):
-            rate, cores, kind, rays, secs, _ = cpu_reference_rate(4, 4, 1)
+            rate, cores, kind, rays, secs, _ = cpu_reference_rate(32, 4, 1)
             out["cpu_baseline"] = {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind,
-                                   "sample": "%dx%d, 16 timed spp in 4 steps (one pass per sample), depth %d, %.1f s of CPU work"
+                                   "sample": "%dx%d, 128 timed spp in 4 steps (one pass per sample), depth %d, %.1f s of CPU work"
                                              % (W, H, DEPTH, secs)}
         print(json.dumps(out))
     if world > 1:

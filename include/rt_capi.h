@@ -41,7 +41,10 @@ typedef struct rt_scene_desc {
 } rt_scene_desc;
 
 enum { RT_RNG_TABLE = 0,      /* the reference's hashed 400 000-float table, kernels/raytracer.cl:113-125 */
-       RT_RNG_COUNTER = 1 };  /* counter-based per-pixel generator — same sampling law */
+       RT_RNG_COUNTER = 1,    /* counter-based per-pixel generator — same sampling law, no table */
+       RT_RNG_COUNTER_TABLE = 2 }; /* the reference's table entered at a counter-keyed uniform index instead of the
+                                 direction hash: the reference's sampling law by construction, two integer hashes
+                                 and one 12-byte gather per bounce */
 enum { RT_ARITH_STRICT = 0,   /* unfused IEEE binary32 in the oracle's operation order (bit-exact arm) */
        RT_ARITH_FAST = 1 };   /* FMA contraction, approximate rcp/rsqrt/sqrt (throughput arm) */
 enum { RT_ACCUM_REFERENCE = 0,/* image = (sqrt(running mean),1), kernels/raytracer.cl:509,524-531 */
@@ -68,7 +71,9 @@ typedef struct rt_stats {
     uint64_t queries_last;    /* nearest-hit queries the last render call actually executed on the device: equal to
                                  rays_last with RT_HEAD_OFF; with RT_HEAD_ON the segments of a path head are traced
                                  once per pixel (when the head is built) instead of once per sample */
-    double   ms_last;         /* device time of the last render call (CUDA events on the context's stream) */
+    double   ms_last;         /* device time of the last render call (CUDA events on the context's stream), including
+                                 the path-head kernels when the call had to rebuild them */
+    double   ms_trace_last;   /* ... of its render kernel (k_trace_*) alone */
     uint32_t samples_done;    /* samples accumulated in the image / accumulation buffer */
     uint32_t kernel_launches; /* kernels launched by this context since creation */
     uint32_t n_primitives;    /* spheres + planes + lenses + triangles on the device */

@@ -72,7 +72,7 @@ struct DevBuf {
 struct rt_ctx {
     int device = 0, W = 0, H = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     float4* d_image = nullptr;
     float4* d_accum_own = nullptr;
     float4* d_accum = nullptr;      // own or caller-supplied
@@ -418,6 +418,7 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     c->stream = c->own_stream;
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "event");
+    if ((e = cudaEventCreate(&c->ev2)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaMalloc(&c->d_image, px * sizeof(float4))) != cudaSuccess) return bail(e, "image buffer");
     if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4))) != cudaSuccess) return bail(e, "accumulation buffer");
     if ((e = cudaMalloc(&c->d_rays, 4 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counters");   // rays, queries, head segments
@@ -446,6 +447,7 @@ int rt_destroy(rt_ctx* c) {
         c->b_tri_mesh.release(); c->b_tri_uv.release(); c->b_tri_face.release(); free_lbvh(c->bvh);
         if (c->ev0) cudaEventDestroy(c->ev0);
         if (c->ev1) cudaEventDestroy(c->ev1);
+        if (c->ev2) cudaEventDestroy(c->ev2);
         if (c->own_stream) cudaStreamDestroy(c->own_stream);
     }
     delete c;
@@ -512,7 +514,7 @@ int rt_set_random_table(rt_ctx* c, const float* table, uint32_t n_floats) {
 int rt_set_params(rt_ctx* c, const rt_params* p) {
     if (!c || !p) return fail(RT_ERR_INVALID, "rt_set_params: null argument");
     if (p->max_depth == 0) return fail(RT_ERR_INVALID, "max_depth must be >= 1");
-    if (p->rng_mode > 1 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2 || p->path_head > 1) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
+    if (p->rng_mode > 2 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2 || p->path_head > 1) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
     c->prm = *p;
     return RT_OK;
 }
@@ -525,7 +527,7 @@ int rt_get_params(rt_ctx* c, rt_params* p) {
 static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, uint32_t accum_mode) {
     if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
     if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
-    if (c->prm.rng_mode == RT_RNG_TABLE && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
+    if (c->prm.rng_mode != RT_RNG_COUNTER && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
     if (c->max_texture_used >= (int64_t)c->tex.layers)
         return fail(RT_ERR_STATE, "render: a textured mesh uses texture %lld but only %d layer(s) are uploaded",
                     (long long)c->max_texture_used, c->tex.layers);
@@ -557,8 +559,10 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
         if (r != RT_OK) return r;
         L.head.rec = c->d_head_rec; L.head.flag = c->d_head_flag; L.head.list = c->d_head_list;
         L.head.n_slots = c->head_n_slots; L.head.n_stoch = c->head_n_stoch;
+        CU(cudaEventRecord(c->ev2, c->stream));
         CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_tail_strict(L, c->stream) : launch_trace_tail_fast(L, c->stream));
     } else {
+        CU(cudaEventRecord(c->ev2, c->stream));
         CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
     }
     CU(cudaEventRecord(c->ev1, c->stream));
@@ -571,6 +575,8 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     // owns the segments of the head although they were traced once.
     const unsigned long long rays = use_head ? (unsigned long long)n * c->head_segments + counters[1] : counters[0];
     c->stats.ms_last = ms;
+    CU(cudaEventElapsedTime(&ms, c->ev2, c->ev1));
+    c->stats.ms_trace_last = ms;
     c->stats.rays_last = rays;
     c->stats.queries_last = use_head ? counters[1] + (head_rebuilt ? c->head_segments : 0ull) : counters[0];
     c->stats.rays_total += rays;
@@ -740,7 +746,7 @@ int rt_bounce_rays(rt_ctx* c, float* rays6, uint32_t n, const uint32_t* sample, 
                    const uint32_t* gx, const uint32_t* gy, float* col3, uint8_t* ended) {
     if (!c || !rays6 || !sample || !bounce || !gx || !gy || !col3 || !ended) return fail(RT_ERR_INVALID, "rt_bounce_rays: null argument");
     if (!c->have_scene) return fail(RT_ERR_STATE, "no scene uploaded");
-    if (c->prm.rng_mode == RT_RNG_TABLE && !c->d_table) return fail(RT_ERR_STATE, "table RNG selected but no random table set");
+    if (c->prm.rng_mode != RT_RNG_COUNTER && !c->d_table) return fail(RT_ERR_STATE, "table RNG selected but no random table set");
     if (n == 0) return RT_OK;
     Guard g(c);
     Scratch s;

@@ -530,10 +530,16 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
     const float extra = m0.y;
     V3 color = mk(m1.x, m1.y, m1.z);
     const uint32_t s_seed = bounce + sample;                        // cl:456,472,476
-    const uint32_t hb = (env.rng_mode == 1u) ? bounce_key(pr.hp, sample, bounce) : 0u;
+    // counter modes: key of this (pixel, sample, bounce); computed only inside the branches that draw
+    auto bounce_hash = [&]() { return bounce_key(pr.hp, sample, bounce); };
 
     if (type == 3 || type == 4) {                                   // diffuse / textured: rayScatter cl:393-399
-        const V3 rv = (env.rng_mode == 0u) ? table_vec<A>(env.table, pr, d, s_seed) : counter_vec<A>(hb);
+        V3 rv;
+        if (env.rng_mode == 2u) {                                   // the reference's table at a counter-keyed uniform index
+            const uint32_t tix = __umulhi(bounce_hash(), RT_TABLE_N);
+            rv = mk(__ldg(env.table + tix), __ldg(env.table + tix + 1), __ldg(env.table + tix + 2));
+        } else if (env.rng_mode == 0u) rv = table_vec<A>(env.table, pr, d, s_seed);
+        else rv = counter_vec<A>(bounce_hash());
         d = A::normalize(vadd<A>(n, rv));
         o = p;
         out = vscale<A>(out, extra);
@@ -559,7 +565,8 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
             float r0 = A::div(A::sub(1.0f, ratio), A::add(1.0f, ratio));   // schlick cl:401-405
             r0 = A::mul(r0, r0);
             const float prob = A::mad(A::sub(1.0f, r0), A::pow5(A::sub(1.0f, -cai)), r0);
-            const float u = (env.rng_mode == 0u) ? table_uniform<A>(env.table, pr, d, s_seed) : u01(draw(hb, 0u));
+            const float u = (env.rng_mode == 2u) ? __ldg(env.table + 3u * RT_TABLE_N + __umulhi(bounce_hash(), RT_TABLE_N))
+                          : (env.rng_mode == 0u) ? table_uniform<A>(env.table, pr, d, s_seed) : u01(draw(bounce_hash(), 0u));
             try_refract = prob < u;                                 // cl:423
         }
         const float disc = A::sub(1.0f, A::mul(A::mul(ratio, ratio), A::sub(1.0f, A::mul(cai, cai))));

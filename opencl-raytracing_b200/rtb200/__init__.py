@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "librtb200.so")
 
-RNG_TABLE, RNG_COUNTER = 0, 1
+RNG_TABLE, RNG_COUNTER, RNG_COUNTER_TABLE = 0, 1, 2
 ARITH_STRICT, ARITH_FAST = 0, 1
 ACCUM_REFERENCE, ACCUM_SUM = 0, 1
 MESH_FIRST_FRONT, MESH_NEAREST = 0, 1
@@ -44,7 +44,7 @@ class Params(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = [("rays_total", C.c_uint64), ("rays_last", C.c_uint64), ("queries_last", C.c_uint64), ("ms_last", C.c_double),
+    _fields_ = [("rays_total", C.c_uint64), ("rays_last", C.c_uint64), ("queries_last", C.c_uint64), ("ms_last", C.c_double), ("ms_trace_last", C.c_double),
                 ("samples_done", C.c_uint32), ("kernel_launches", C.c_uint32), ("n_primitives", C.c_uint32),
                 ("bvh_nodes", C.c_uint32)]
 

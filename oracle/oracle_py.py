@@ -131,7 +131,7 @@ class OrcHit(C.Structure):
                 ("uv", C.c_float * 2), ("mat_id", C.c_uint32), ("texture_id", C.c_uint32)]
 
 
-RNG_TABLE, RNG_COUNTER = 0, 1
+RNG_TABLE, RNG_COUNTER, RNG_COUNTER_TABLE = 0, 1, 2
 ACCUM_REFERENCE, ACCUM_SUM = 0, 1
 MESH_FIRST_FRONT, MESH_NEAREST = 0, 1
 

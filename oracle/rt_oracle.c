@@ -373,13 +373,17 @@ static int shade(const ctx_t* c, const orc_hit* h, v3* o, v3* d, v3* out, uint32
     v3 color = vld(m->color);
     uint32_t s_seed = bounce + sample;                                   /* cl:456,472,476 */
     uint32_t hb = 0;
-    if (c->prm->rng_mode == ORC_RNG_COUNTER)
+    if (c->prm->rng_mode != ORC_RNG_TABLE)
         hb = orc_rng_bounce_key(c->prm->seed, c->gy * c->W + c->gx, sample, bounce);
+    /* ORC_RNG_COUNTER_TABLE: the reference's own table (so its sampling law by construction, misaligned read
+     * included, cl:109-117), entered at a counter-keyed uniform index instead of the direction hash. */
+    uint32_t tix = (uint32_t)(((uint64_t)hb * TABLE_N) >> 32);
     switch (m->type) {
     case M_DIFFUSE:
     case M_TEXTURED: {                                                   /* cl:393-399 rayScatter */
         v3 rv;
         if (c->prm->rng_mode == ORC_RNG_TABLE) rv = table_vec(c->table, *d, s_seed, c->gx, c->gy);
+        else if (c->prm->rng_mode == ORC_RNG_COUNTER_TABLE) rv = V(c->table[tix], c->table[tix + 1], c->table[tix + 2]);
         else { float r3[3]; orc_rng_scatter_vec(hb, r3); rv = vld(r3); }
         *d = vnormalize(vadd(n, rv));
         *o = p;
@@ -410,7 +414,7 @@ static int shade(const ctx_t* c, const orc_hit* h, v3* o, v3* d, v3* out, uint32
             r0 *= r0;
             float prob = r0 + (1.0f - r0) * powf(1.0f - cosi, 5.0f);
             float u = (c->prm->rng_mode == ORC_RNG_TABLE) ? table_uniform(c->table, *d, s_seed, c->gx, c->gy)
-                                                          : orc_rng_uniform(hb);
+                    : (c->prm->rng_mode == ORC_RNG_COUNTER_TABLE) ? c->table[3u * TABLE_N + tix] : orc_rng_uniform(hb);
             try_refract = prob < u;                                      /* cl:423 */
         }
         float disc = 1.0f - ratio * ratio * (1.0f - cai * cai);

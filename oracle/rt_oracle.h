@@ -27,7 +27,7 @@ typedef struct orc_scene_desc {
     uint32_t n_materials, n_spheres, n_planes, n_lenses, n_vertices, n_uvs, n_indices, n_meshes, n_models;
 } orc_scene_desc;
 
-enum { ORC_RNG_TABLE = 0, ORC_RNG_COUNTER = 1 };
+enum { ORC_RNG_TABLE = 0, ORC_RNG_COUNTER = 1, ORC_RNG_COUNTER_TABLE = 2 };
 enum { ORC_ACCUM_REFERENCE = 0, ORC_ACCUM_SUM = 1 };
 enum { ORC_MESH_FIRST_FRONT = 0, ORC_MESH_NEAREST = 1 };
 

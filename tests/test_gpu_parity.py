@@ -187,6 +187,33 @@ def test_counter_rng_strict_bit_exact_and_same_law(rt, port, scenes, table):
         assert abs(float((img[..., :3] ** 2).mean()) - float((t_a[..., :3] ** 2).mean())) <= 0.004
 
 
+def test_counter_table_rng_strict_bit_exact_and_same_law(rt, port, scenes, table):
+    """RT_RNG_COUNTER_TABLE (bench.py's generator): the reference's table entered at a counter-keyed index.  Strict
+    arithmetic is bit-exact against the oracle's restatement; block means agree with the reference's table mode as
+    well as two table seeds agree with each other."""
+    from rtb200 import fixtures as fx
+    W, H, spp = 320, 240, 64
+    arr, tex = scenes["default"]
+    d = op.make_desc(arr)
+    cam = fx.camera(60, W / H)
+    want, rays_want, _ = port.render(d, tex, cam, table, W, H, 0, spp, port.params(max_depth=30, rng_mode=op.RNG_COUNTER_TABLE, seed=77))
+    with make_ctx(rt, scenes, "default", W, H, table, max_depth=30, arith=rt.ARITH_STRICT, rng_mode=rt.RNG_COUNTER_TABLE, seed=77) as ctx:
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        got = ctx.read_image()
+        assert n_diff_pixels(got, want) <= 3
+        assert abs(int(ctx.stats().rays_last) - int(rays_want)) <= 60
+        ctx.set_params(max_depth=30, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=78)
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
+        fast_c = ctx.read_image()
+    t_a, _, _ = port.render(d, tex, cam, table, W, H, 0, spp, port.params(max_depth=30))
+    t_b, _, _ = port.render(d, tex, cam, port.make_table(999), W, H, 0, spp, port.params(max_depth=30))
+    noise = np.sqrt(((block_means(t_a) - block_means(t_b)) ** 2).mean())
+    for img in (got, fast_c):
+        err = np.sqrt(((block_means(img) - block_means(t_a)) ** 2).mean())
+        assert err <= 2.0 * noise, (err, noise)
+        assert abs(float((img[..., :3] ** 2).mean()) - float((t_a[..., :3] ** 2).mean())) <= 0.004
+
+
 def test_sample_split_sums_to_whole(rt, scenes, table):
     """What the multi-GPU split relies on: disjoint global sample ranges accumulate to the single-launch sum."""
     from rtb200 import fixtures as fx
