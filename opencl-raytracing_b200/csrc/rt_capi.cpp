@@ -544,8 +544,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
     L.queries = c->d_rays + 1;
-    // Path heads: brute-force scenes (the LBVH kernels still trace every segment of every sample).
-    const bool use_head = c->prm.path_head == RT_HEAD_ON && c->bvh.n_leaves == 0;
+    const bool use_head = c->prm.path_head == RT_HEAD_ON;
     if (!use_head && c->prm.arith == RT_ARITH_FAST) {
         int r = ensure_certified(c, cam);
         if (r != RT_OK) return r;

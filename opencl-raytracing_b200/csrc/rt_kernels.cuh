@@ -930,6 +930,108 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
 }
 
+// LBVH flavour of trace_tail_body: lanes advance ONE node per trip of the traversal loop (see trace_body_bvh); a lane
+// whose traversal finished waits until `regen` lanes wait, then the waiting lanes close their path on a miss / light,
+// or shade the hit and start the bounced ray; finished paths restart from the stored head.
+template <class A>
+__device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
+    const uint32_t stoch_blocks = (p.head.n_stoch + kTraceThreads - 1u) / kTraceThreads;
+    if (blockIdx.x >= stoch_blocks) { terminal_body<A>(p, (blockIdx.x - stoch_blocks) * kTraceThreads + threadIdx.x); return; }
+    __shared__ float4 hs_all[4 * kTraceThreads];
+    float4* hs = hs_all + threadIdx.x;
+    const float4* S = p.sc.stream;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t j = blockIdx.x * kTraceThreads + threadIdx.x;
+    const bool live = j < p.head.n_stoch;
+    const uint32_t slot = live ? __ldg(p.head.list + j) : 0u;
+    int x, y;
+    slot_pixel(slot, p.W, x, y);
+#pragma unroll
+    for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
+
+    const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
+    ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
+    float4* px = p.target + (size_t)y * p.W + x;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (live && (p.accum_mode == 1u || p.first > 0u)) acc = *px;
+    const uint32_t k_end = p.first + p.n;
+    uint32_t k = live ? p.first : k_end, i, mat_id;
+    V3 o, d, out;
+    Hit h;
+    auto restart = [&]() {
+        const float4 r0 = hs[0], r1 = hs[kTraceThreads], r2 = hs[2 * kTraceThreads], r3 = hs[3 * kTraceThreads];
+        o = mk(r0.x, r0.y, r0.z); d = mk(r1.x, r1.y, r1.z); out = mk(r2.x, r2.y, r2.z);
+        h.t = r0.w; h.bu = r1.w; h.bv = r2.w;
+        i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
+    };
+    restart();
+    uint32_t queries = 0u;
+    const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
+    V3 inv = mk(0.0f, 0.0f, 0.0f);
+    int stack[64];
+    int sp = 0, node = 0;
+    bool traversing = false, has_ray = k < k_end, have_result = false;
+    auto start_ray = [&]() {
+        h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
+        hit_planes<A>(p.sc, S, o, d, h);
+        sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
+        if (traversing && node < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~node)), o, d, h); traversing = false; }
+        inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+        have_result = true;
+    };
+
+    while (__any_sync(RT_FULL, has_ray)) {
+        if (has_ray && !traversing) {                        // ---- waiting lanes: close, shade, bounce, restart
+            if (have_result) {
+                ++queries;
+                bool ended = false;
+                if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }      // cl:450-452
+                else {
+                    mat_id = hit_material(p.sc, S, h);
+                    if (__float_as_int(__ldg(p.sc.mat + 2 * mat_id).x) == 5) {          // light, cl:459-462
+                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                        out = vmin(out, mk(m1.x, m1.y, m1.z));
+                        ended = true;
+                    }
+                }
+                if (ended) { accumulate_sample<A>(acc, out, k, p.accum_mode); ++k; has_ray = k < k_end; restart(); }
+            }
+            while (has_ray) {
+                shade<A>(env, S, h, mat_id, pr, o, d, out, k, i);
+                if (++i < p.depth) { start_ray(); break; }
+                accumulate_sample<A>(acc, out, k, p.accum_mode);                         // cl:447: depth exhausted, keep out
+                ++k; has_ray = k < k_end; restart();
+            }
+        }
+        for (;;) {                                           // ---- traversal: one node per trip
+            if (traversing) {
+                const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
+                const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+                const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
+                const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
+                float t0, t1;
+                bool h0 = slab(lo0, hi0, o, inv, h.t, t0), h1 = slab(lo1, hi1, o, inv, h.t, t1);
+                if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
+                if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
+                if (h0 && h1) {
+                    const bool first0 = t0 <= t1;
+                    if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+                    node = first0 ? c0 : c1;
+                } else if (h0) node = c0;
+                else if (h1) node = c1;
+                else if (sp > 0) node = stack[--sp];
+                else traversing = false;
+            }
+            const unsigned trav = __ballot_sync(RT_FULL, traversing);
+            const unsigned waiting = __ballot_sync(RT_FULL, has_ray && !traversing);
+            if (trav == 0u || (uint32_t)__popc(waiting) >= regen) break;
+        }
+    }
+    if (live) *px = acc;
+    queries = __reduce_add_sync(RT_FULL, queries);
+    if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
+}
+
 // Nearest hit of arbitrary rays (rays6 != nullptr) or of the primary rays of the frame; same code path as the
 // render loop (warp-cooperative meshes, optional certification of primary hits).
 template <class A, bool BVH>

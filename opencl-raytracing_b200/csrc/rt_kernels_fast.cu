@@ -17,6 +17,9 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_tra
     extern __shared__ float4 smem[];
     trace_tail_body<Fused>(p, smem);
 }
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_fast_bvh(const __grid_constant__ TraceLaunch p) {
+    trace_tail_bvh_body<Fused>(p);
+}
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
     probe_hits_body<Fused, false>(p, smem);
@@ -36,7 +39,8 @@ cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_trace_fast_bvh, p, tiles * 32, s, true) : launch_staged(k_trace_fast, p, tiles * 32, s);
 }
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s) {
-    return launch_staged(k_trace_tail_fast, p, tail_work_items(p), s, false, kHeadStateBytes);
+    return p.bvh.n_leaves ? launch_staged(k_trace_tail_fast_bvh, p, tail_work_items(p), s, true)
+                          : launch_staged(k_trace_tail_fast, p, tail_work_items(p), s, false, kHeadStateBytes);
 }
 cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_probe_hits_fast_bvh, p, p.n, s, true) : launch_staged(k_probe_hits_fast, p, p.n, s);

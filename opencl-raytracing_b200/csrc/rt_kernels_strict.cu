@@ -22,6 +22,9 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_strict(
     extern __shared__ float4 smem[];
     trace_tail_body<Exact>(p, smem);
 }
+extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_strict_bvh(const __grid_constant__ TraceLaunch p) {
+    trace_tail_bvh_body<Exact>(p);
+}
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_strict(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
     probe_hits_body<Exact, false>(p, smem);
@@ -44,7 +47,8 @@ cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_head_bvh, p, p.n_slots, s, true) : launch_staged(k_head, p, p.n_slots, s);
 }
 cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s) {
-    return launch_staged(k_trace_tail_strict, p, tail_work_items(p), s, false, kHeadStateBytes);
+    return p.bvh.n_leaves ? launch_staged(k_trace_tail_strict_bvh, p, tail_work_items(p), s, true)
+                          : launch_staged(k_trace_tail_strict, p, tail_work_items(p), s, false, kHeadStateBytes);
 }
 cudaError_t launch_probe_hits_strict(const ProbeLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_probe_hits_strict_bvh, p, p.n, s, true) : launch_staged(k_probe_hits_strict, p, p.n, s);

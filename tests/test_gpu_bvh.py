@@ -119,3 +119,28 @@ def test_bvh_image_bit_exact_and_certified(port):
         fast = ctx.read_image()
     w16, _, _ = port.render(d, None, cam, None, W, H, 0, 16, prm)
     assert abs(float((fast[..., :3] ** 2).mean()) - float((w16[..., :3] ** 2).mean())) < 5e-3
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+def test_bvh_path_heads_change_nothing(arith):
+    """LBVH render kernels with and without path heads: identical strict bits and segment counts."""
+    import rtb200 as rt
+    from rtb200 import fixtures as fx, synth
+    arrays, _ = synth.scene(n_spheres=300, mesh_subdiv=4, seed=5)
+    W, H, depth = 192, 108, 6
+    cam = fx.camera(60, W / H)
+    A = rt.ARITH_STRICT if arith == "strict" else rt.ARITH_FAST
+    res = {}
+    for mode in (rt.HEAD_OFF, rt.HEAD_ON):
+        with rt.Context(W, H) as ctx:
+            ctx.set_params(max_depth=depth, rng_mode=rt.RNG_COUNTER, seed=3, arith=A, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BVH, path_head=mode)
+            ctx.upload_scene(arrays)
+            ctx.render_samples(cam, 0, 5, rt.ACCUM_REFERENCE)
+            st = ctx.stats()
+            res[mode] = (ctx.read_image().copy(), st.rays_last, st.queries_last)
+    off, on = res[rt.HEAD_OFF], res[rt.HEAD_ON]
+    assert off[1] == off[2] and on[2] < on[1]
+    if arith == "strict":
+        assert np.array_equal(bits(on[0]), bits(off[0])) and on[1] == off[1]
+    else:
+        assert abs(float((on[0][..., :3] ** 2).mean()) - float((off[0][..., :3] ** 2).mean())) < 5e-3
