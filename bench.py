@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--arith", default="fast", choices=["fast", "strict"])
     ap.add_argument("--rng", default="counter_table", choices=["counter_table", "counter", "table"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reduce", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: fused = every rank reduces+finalizes its rows out of the peers' buffers (CUDA IPC over NVLink, "
+                         "rt_finalize_peers); nccl = one torch.distributed reduce to rank 0 + rt_finalize")
     ap.add_argument("--no-heads", action="store_true", help="RT_HEAD_OFF: trace every segment of every sample (A/B of the path-head memoisation)")
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"],
                     help="BASELINE.json configs; the driver's default (and the headline) is c2")
@@ -204,10 +207,14 @@ def main_b200(a):
     ctx.upload_textures(tex); ctx.upload_scene(arr); ctx.set_random_table(table)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-    ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
+    fused = world > 1 and a.reduce == "fused"
+    accum = None
+    if not fused:          # torch-owned buffer (what dist.reduce needs); the fused path exports the context's own buffer
+        accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
-    from rtb200.multigpu import reduce_to_rank0, sample_range
+    from rtb200.multigpu import PeerFinalize, reduce_to_rank0, sample_range
+    peers = PeerFinalize(ctx) if fused else None
     spp = a.spp
     first, n_mine = sample_range(spp, world, rank)
 
@@ -216,15 +223,21 @@ def main_b200(a):
     queries_steps = []
 
     def step():
-        accum.zero_()
+        if fused:
+            ctx.clear_accum()
+        else:
+            accum.zero_()
         ctx.invalidate_caches()          # every step rebuilds the path heads: nothing is carried over between steps
         ctx.render_samples(cam, first, n_mine, rtb200.ACCUM_SUM)
         st = ctx.stats()
         rays, kms = st.rays_last, st.ms_trace_last
         queries_steps.append(st.queries_last)
-        reduce_to_rank0(accum)
-        if rank == 0:
-            ctx.finalize(spp)
+        if fused:
+            peers.finalize(spp)
+        else:
+            reduce_to_rank0(accum)
+            if rank == 0:
+                ctx.finalize(spp)
         return rays, kms
 
     def sync_all():
@@ -313,7 +326,8 @@ def main_b200(a):
             "warmup": a.warmup, "ms_per_step": round(elapsed_ms / a.steps, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "spp_total": spp, "spp_per_gpu": n_mine, "arith": a.arith, "rng": a.rng,
-                       "parallelism": "spp-split x%d + 1 NCCL reduce" % world if world > 1 else "single GPU",
+                       "parallelism": ("spp-split x%d + %s" % (world, "fused peer-memory reduce+finalize (rt_finalize_peers)" if fused else "1 NCCL reduce"))
+                                      if world > 1 else "single GPU",
                        "l2": "flushed between steps (256 MiB memset); inputs are < 40 MB, the kernel is issue bound",
                        "rays_per_step": int(rays_total / a.steps),
                        "ray": "one path segment = one hitScene call of the reference (kernels/raytracer.cl:322-360); the image is the "

@@ -132,6 +132,21 @@ int rt_accum_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
 int rt_image_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
 int rt_set_accum_device_buffer(rt_ctx* ctx, void* device_ptr, size_t bytes);
 
+/* Fused reduce + finalize over NVLink peer memory (the exchange step of the sample split; the reference has no
+ * multi-device code).  Every rank exports its accumulation buffer (and rank 0 its image) as CUDA IPC handles
+ * (64 bytes each); after the handles of all ranks were exchanged (torch.distributed / any transport) and opened,
+ * rt_finalize_peers on rank r sums rows [H*r/N, H*(r+1)/N) of ALL ranks' accumulation buffers through peer loads,
+ * applies the tail of kernels/raytracer.cl:509,531 (divide by spp, sqrt) and stores the pixels straight into rank
+ * 0's image: reduce-scatter + gather + finalize in one kernel per rank, every NVLink used, no staging buffer.
+ * The caller synchronises the ranks before (all renders finished) and after (all slices written).
+ * rt_set_peers_direct is the same with plain device pointers (several contexts inside one process). */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_ipc_export(rt_ctx* ctx, void* accum_handle, void* image_handle);
+int rt_ipc_open_peers(rt_ctx* ctx, int n_ranks, int my_rank, const void* accum_handles, const void* image_handle_rank0);
+int rt_set_peers_direct(rt_ctx* ctx, int n_ranks, int my_rank, void* const* accum_ptrs, void* image_rank0);
+int rt_finalize_peers(rt_ctx* ctx, uint32_t total_spp);
+int rt_close_peers(rt_ctx* ctx);
+
 /* Probes used by the parity tests: nearest hit of arbitrary rays, and one bounce of the path loop.
  * rays6 = n x (origin.xyz, dir.xyz) on the host.  out_t/out_id may be NULL. */
 int rt_trace_rays(rt_ctx* ctx, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t);

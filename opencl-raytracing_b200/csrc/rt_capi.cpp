@@ -109,6 +109,12 @@ struct rt_ctx {
     float head_cam[12] = {0};
     uint32_t head_mesh_mode = 0, head_depth = 0;
     bool head_bvh = false, head_valid = false;
+    // peers of the sample split (rt_ipc_open_peers / rt_set_peers_direct)
+    int peer_n = 0, peer_rank = 0;
+    void* peer_accum[kMaxPeers] = {nullptr};
+    void* peer_image0 = nullptr;
+    bool peer_opened[kMaxPeers] = {false};   // accum pointers obtained from cudaIpcOpenMemHandle
+    bool peer_image_opened = false;
     rt_stats stats{};
 };
 
@@ -439,6 +445,7 @@ int rt_destroy(rt_ctx* c) {
     {
         Guard g(c);
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+        rt_close_peers(c);
         cudaFree(c->d_certify);
         cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
@@ -668,6 +675,84 @@ int rt_set_accum_device_buffer(rt_ctx* c, void* p, size_t bytes) {
     if (bytes < (size_t)c->W * c->H * sizeof(float4)) return fail(RT_ERR_INVALID, "accumulation buffer too small");
     if (((uintptr_t)p & 15u) != 0) return fail(RT_ERR_INVALID, "accumulation buffer must be 16-byte aligned");
     c->d_accum = (float4*)p;
+    return RT_OK;
+}
+
+// ---- fused reduce + finalize over peer memory --------------------------------------------------
+int rt_close_peers(rt_ctx* c) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    Guard g(c);
+    for (int r = 0; r < kMaxPeers; ++r) {
+        if (c->peer_opened[r] && c->peer_accum[r]) cudaIpcCloseMemHandle(c->peer_accum[r]);
+        c->peer_accum[r] = nullptr; c->peer_opened[r] = false;
+    }
+    if (c->peer_image_opened && c->peer_image0) cudaIpcCloseMemHandle(c->peer_image0);
+    c->peer_image0 = nullptr; c->peer_image_opened = false;
+    c->peer_n = 0;
+    return RT_OK;
+}
+int rt_ipc_export(rt_ctx* c, void* accum_handle, void* image_handle) {
+    if (!c || !accum_handle || !image_handle) return fail(RT_ERR_INVALID, "rt_ipc_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    if (c->d_accum != c->d_accum_own) return fail(RT_ERR_STATE, "rt_ipc_export: the context accumulates into a caller buffer; only the context's own buffer can be exported");
+    Guard g(c);
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c->d_accum_own));
+    std::memcpy(accum_handle, &h, sizeof h);
+    CU(cudaIpcGetMemHandle(&h, c->d_image));
+    std::memcpy(image_handle, &h, sizeof h);
+    return RT_OK;
+}
+int rt_ipc_open_peers(rt_ctx* c, int n, int rank, const void* accum_handles, const void* image_handle0) {
+    if (!c || !accum_handles || !image_handle0) return fail(RT_ERR_INVALID, "rt_ipc_open_peers: null argument");
+    if (n < 1 || n > kMaxPeers || rank < 0 || rank >= n) return fail(RT_ERR_INVALID, "rt_ipc_open_peers: bad rank %d of %d (max %d)", rank, n, kMaxPeers);
+    rt_close_peers(c);
+    Guard g(c);
+    for (int r = 0; r < n; ++r) {
+        if (r == rank) { c->peer_accum[r] = c->d_accum_own; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, (const char*)accum_handles + (size_t)r * sizeof h, sizeof h);
+        CU(cudaIpcOpenMemHandle(&c->peer_accum[r], h, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_opened[r] = true;
+    }
+    if (rank == 0) c->peer_image0 = c->d_image;
+    else {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, image_handle0, sizeof h);
+        CU(cudaIpcOpenMemHandle(&c->peer_image0, h, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_image_opened = true;
+    }
+    c->peer_n = n; c->peer_rank = rank;
+    return RT_OK;
+}
+int rt_set_peers_direct(rt_ctx* c, int n, int rank, void* const* accum_ptrs, void* image0) {
+    if (!c || !accum_ptrs || !image0) return fail(RT_ERR_INVALID, "rt_set_peers_direct: null argument");
+    if (n < 1 || n > kMaxPeers || rank < 0 || rank >= n) return fail(RT_ERR_INVALID, "rt_set_peers_direct: bad rank %d of %d (max %d)", rank, n, kMaxPeers);
+    rt_close_peers(c);
+    for (int r = 0; r < n; ++r) {
+        if (!accum_ptrs[r]) return fail(RT_ERR_INVALID, "rt_set_peers_direct: null buffer for rank %d", r);
+        c->peer_accum[r] = accum_ptrs[r];
+    }
+    c->peer_image0 = image0;
+    c->peer_n = n; c->peer_rank = rank;
+    return RT_OK;
+}
+int rt_finalize_peers(rt_ctx* c, uint32_t spp) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize_peers: spp must be > 0");
+    if (c->peer_n < 1) return fail(RT_ERR_STATE, "rt_finalize_peers: no peers set (rt_ipc_open_peers / rt_set_peers_direct)");
+    Guard g(c);
+    PeerFinalize P{};
+    for (int r = 0; r < c->peer_n; ++r) P.accum[r] = (const float4*)c->peer_accum[r];
+    P.image = (float4*)c->peer_image0;
+    P.n_ranks = c->peer_n;
+    const long long px = (long long)c->W * c->H;
+    P.first_pixel = (int)(px * c->peer_rank / c->peer_n);
+    P.n_pixels = (int)(px * (c->peer_rank + 1) / c->peer_n) - P.first_pixel;
+    P.inv_spp = 1.0f / (float)spp;
+    CU(launch_finalize_peers(P, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.kernel_launches += 1;
     return RT_OK;
 }
 

@@ -143,6 +143,15 @@ cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s);
 // list = slots partitioned by flag == kHeadStochastic (CUB DevicePartition); *n_stoch on the device
 cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s);
 cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);
+constexpr int kMaxPeers = 16;
+struct PeerFinalize {          // k_finalize_peers: sum of n_ranks accumulation buffers -> image of rank 0
+    const float4* accum[kMaxPeers];
+    float4* image;
+    int n_ranks;
+    int first_pixel, n_pixels;
+    float inv_spp;
+};
+cudaError_t launch_finalize_peers(const PeerFinalize& p, cudaStream_t s);
 cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t s);
 
 }  // namespace rtb

@@ -20,6 +20,26 @@ cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, ui
     return cudaGetLastError();
 }
 
+// Fused reduce-scatter + finalize + gather over peer memory: this rank's slice of the frame, summed over the
+// accumulation buffers of all ranks (peer loads over NVLink, 16 B per lane, coalesced; ranks in fixed order so the
+// sum is deterministic), divided by spp, square-rooted, stored into rank 0's image (peer store).
+__global__ void __launch_bounds__(256) k_finalize_peers(const __grid_constant__ PeerFinalize p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_pixels) return;
+    const int px = p.first_pixel + i;
+    float4 a = p.accum[0][px];
+    for (int r = 1; r < p.n_ranks; ++r) {
+        const float4 b = p.accum[r][px];
+        a.x += b.x; a.y += b.y; a.z += b.z;
+    }
+    p.image[px] = make_float4(sqrtf(a.x * p.inv_spp), sqrtf(a.y * p.inv_spp), sqrtf(a.z * p.inv_spp), 1.0f);
+}
+cudaError_t launch_finalize_peers(const PeerFinalize& p, cudaStream_t s) {
+    if (p.n_pixels <= 0) return cudaSuccess;
+    k_finalize_peers<<<(p.n_pixels + 255) / 256, 256, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 // Slots with a stochastic path head to the front of `list` (in slot order), all others to the back (reversed).
 struct IsStochastic {
     const uint8_t* flag;

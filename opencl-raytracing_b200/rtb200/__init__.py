@@ -75,6 +75,8 @@ def lib():
         "rt_image_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
         "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
+        "rt_ipc_export": [vp, vp, vp], "rt_ipc_open_peers": [vp, ci, ci, vp, vp],
+        "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_close_peers": [vp],
         "rt_measure_fp32_peak": [ci, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rt_scene_load": [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)], "rt_scene_get_desc": [vp, C.POINTER(SceneDesc)],
         "rt_scene_get_textures": [vp, C.POINTER(vp), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)],
@@ -269,6 +271,26 @@ class Context:
 
     def set_accum_device_buffer(self, ptr, nbytes):
         _check(self.L.rt_set_accum_device_buffer(self.h, ptr, nbytes))
+
+    def ipc_export(self):
+        """-> (accum handle, image handle), 64 bytes each (CUDA IPC)."""
+        a, i = C.create_string_buffer(64), C.create_string_buffer(64)
+        _check(self.L.rt_ipc_export(self.h, a, i))
+        return a.raw, i.raw
+
+    def ipc_open_peers(self, rank, accum_handles, image_handle_rank0):
+        blob = b"".join(accum_handles)
+        _check(self.L.rt_ipc_open_peers(self.h, len(accum_handles), rank, blob, image_handle_rank0))
+
+    def set_peers_direct(self, rank, accum_ptrs, image_ptr_rank0):
+        arr = (C.c_void_p * len(accum_ptrs))(*accum_ptrs)
+        _check(self.L.rt_set_peers_direct(self.h, len(accum_ptrs), rank, arr, image_ptr_rank0))
+
+    def finalize_peers(self, spp):
+        _check(self.L.rt_finalize_peers(self.h, spp))
+
+    def close_peers(self):
+        _check(self.L.rt_close_peers(self.h))
 
     def trace_rays(self, rays6):
         r = np.ascontiguousarray(rays6, dtype=np.float32).reshape(-1, 6)

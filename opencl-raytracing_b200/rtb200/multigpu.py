@@ -7,6 +7,11 @@ tail (divide by spp, sqrt) with rt_finalize.  Because sample indices are global 
 (pixel, sample, bounce), the picture does not depend on `world` beyond float summation order."""
 from __future__ import annotations
 
+# Two exchange steps are provided:
+#   reduce_to_rank0      one NCCL sum-reduce of the buffers (torch.distributed), rt_finalize on rank 0;
+#   PeerFinalize         fused: every rank reduces + finalizes its slice of rows straight out of the peers'
+#                        buffers (CUDA IPC over NVLink) into rank 0's image — rt_finalize_peers.
+
 
 def sample_range(spp: int, world: int, rank: int):
     """-> (first, count): contiguous, disjoint, covering [0, spp); counts differ by at most one."""
@@ -22,3 +27,26 @@ def reduce_to_rank0(accum, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM, group=group)
     return accum
+
+
+class PeerFinalize:
+    """Fused reduce + finalize over peer memory.  Handles are exchanged once (all_gather_object); per render every
+    rank calls finalize(spp) between two barriers."""
+
+    def __init__(self, ctx, group=None):
+        import torch.distributed as dist
+        self.ctx, self.group = ctx, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        mine = ctx.ipc_export()
+        allh = [None] * self.world
+        dist.all_gather_object(allh, mine, group=group)
+        ctx.ipc_open_peers(self.rank, [h[0] for h in allh], allh[0][1])
+
+    def finalize(self, spp):
+        import torch.distributed as dist
+        dist.barrier(group=self.group)       # every rank's render has finished (render calls are synchronous)
+        self.ctx.finalize_peers(spp)
+        dist.barrier(group=self.group)       # every slice of rank 0's image has been written
+
+    def close(self):
+        self.ctx.close_peers()

@@ -303,3 +303,40 @@ def test_path_heads_change_nothing(rt, scenes, table, name, W, H, depth, arith):
         assert abs(float((on[0][..., :3] ** 2).mean()) - float((off[0][..., :3] ** 2).mean())) < 5e-3
         assert abs(on[1] - off[1]) <= 1e-3 * off[1]
         assert np.all(on[3][..., 3] == 5.0) and np.all(off[3][..., 3] == 5.0)
+
+
+def test_fused_peer_finalize_equals_reduce_then_finalize(rt, scenes, table):
+    """rt_finalize_peers (the fused exchange step of the sample split): three 'ranks' as three contexts on this GPU,
+    disjoint global sample ranges, every rank finalizes its slice of rows out of all accumulation buffers into rank
+    0's image.  Must equal sum -> rt_finalize of a single context rendering all samples (float summation order aside)."""
+    from rtb200 import fixtures as fx
+    from rtb200.multigpu import sample_range
+    W, H, spp, world = 250, 131, 12, 3
+    cam = fx.camera(60, W / H)
+    kw = dict(max_depth=30, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=9)
+    ctxs = [make_ctx(rt, scenes, "default", W, H, table, **kw) for _ in range(world)]
+    try:
+        for r, c in enumerate(ctxs):
+            first, n = sample_range(spp, world, r)
+            c.clear_accum()
+            c.render_samples(cam, first, n, rt.ACCUM_SUM)
+        ptrs = [c.accum_device_ptr()[0] for c in ctxs]
+        img0 = ctxs[0].image_device_ptr()[0]
+        for r, c in enumerate(ctxs):
+            c.set_peers_direct(r, ptrs, img0)
+        for c in ctxs:
+            c.finalize_peers(spp)
+        got = ctxs[0].read_image()
+        with make_ctx(rt, scenes, "default", W, H, table, **kw) as one:
+            one.clear_accum()
+            one.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+            one.finalize(spp)
+            want = one.read_image()
+        assert np.all(got[..., 3] == 1.0)
+        assert np.abs(got - want).max() <= 2e-6
+        with pytest.raises(rt.RtError):
+            ctxs[1].close_peers()
+            ctxs[1].finalize_peers(spp)
+    finally:
+        for c in ctxs:
+            c.close()
