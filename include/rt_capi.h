@@ -125,6 +125,12 @@ int rt_read_image(rt_ctx* ctx, float* rgba);                  /* width*height*4 
 int rt_read_accum(rt_ctx* ctx, float* rgba);                  /* width*height*4 floats */
 int rt_read_primary_ids(rt_ctx* ctx, const float camera[12], uint32_t* ids, float* t);
 int rt_get_stats(rt_ctx* ctx, rt_stats* stats);
+/* Checkpoint / resume of the progressive state (the reference keeps it only in the GL texture + sample_counter,
+ * include/raytracer.h:21, and loses it on exit).  rt_restore_image puts back an image read with rt_read_image together
+ * with the number of samples it holds, so that rt_render_again continues the sqrt(mean) chain bit for bit;
+ * rt_restore_accum does the same for the linear accumulation buffer. */
+int rt_restore_image(rt_ctx* ctx, const float* rgba, uint32_t samples_in_image);
+int rt_restore_accum(rt_ctx* ctx, const float* rgba, uint32_t samples_in_buffer);
 
 /* Device-side access for the multi-GPU sample split (one process per GPU; the caller reduces the buffer with
  * NCCL): pointer to the W*H float4 accumulation buffer, or make the context accumulate into a caller buffer. */

@@ -652,6 +652,24 @@ int rt_read_accum(rt_ctx* c, float* rgba) {
     CU(cudaStreamSynchronize(c->stream));
     return RT_OK;
 }
+int rt_restore_image(rt_ctx* c, const float* rgba, uint32_t samples) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_restore_image: null argument");
+    if (samples == 0) return fail(RT_ERR_INVALID, "rt_restore_image: an image holds at least one sample");
+    Guard g(c);
+    CU(cudaMemcpyAsync(c->d_image, rgba, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->sample_counter = samples - 1u;          // rt_render_again renders sample index sample_counter + 1
+    c->stats.samples_done = samples;
+    return RT_OK;
+}
+int rt_restore_accum(rt_ctx* c, const float* rgba, uint32_t samples) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_restore_accum: null argument");
+    Guard g(c);
+    CU(cudaMemcpyAsync(c->d_accum, rgba, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->stats.samples_done = samples;
+    return RT_OK;
+}
 int rt_get_stats(rt_ctx* c, rt_stats* s) {
     if (!c || !s) return fail(RT_ERR_INVALID, "rt_get_stats: null argument");
     *s = c->stats;

@@ -6,6 +6,9 @@
 //   rt_headless [--scene F] [--root DIR] [--textures DIR] [--width W] [--height H] [--spp N] [--depth D]
 //               [--arith strict|fast] [--rng table|counter] [--table-seed S] [--fov DEG] [--pos x,y,z]
 //               [--yaw DEG] [--pitch DEG] [--script FILE] [--out img.tga] [--raw img.f32]
+//               [--checkpoint FILE] [--resume FILE]
+//   checkpoint file: "RTCK" u32 width, height, samples, then width*height*4 float32 of the (sqrt(mean),1) image; --resume
+//   restores it (rt_restore_image) and continues with renderAgain, bit-identical to an uninterrupted run
 //   script lines:  move forward|back|left|right DT | rotate DX DY | zoom SCROLL | fast 0|1 | slow 0|1 | frames N
 #include <chrono>
 #include <cstdio>
@@ -21,7 +24,7 @@
 int main(int argc, char** argv) {
     int W = 1200, H = 800, spp = 16, fov = 60;   // main.cpp:10-11,65 (SCR_WIDTH x SCR_HEIGHT, fov 60)
     float pos[3] = {0, 0, 0}, yaw = 0, pitch = 0;
-    std::string out_tga, out_raw, script;
+    std::string out_tga, out_raw, script, ckpt_out, ckpt_in;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto val = [&]() -> const char* { if (i + 1 >= argc) { std::fprintf(stderr, "missing value for %s\n", a.c_str()); std::exit(2); } return argv[++i]; };
@@ -42,12 +45,28 @@ int main(int argc, char** argv) {
         else if (a == "--script") script = val();
         else if (a == "--out") out_tga = val();
         else if (a == "--raw") out_raw = val();
+        else if (a == "--checkpoint") ckpt_out = val();
+        else if (a == "--resume") ckpt_in = val();
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
     Camera camera(fov, (float)W / (float)H, glm::vec3(pos[0], pos[1], pos[2]), yaw, pitch);
     RayTracer tracer(W, H, "kernels/raytracer.cl");
 
     bool camera_in_motion = true;                       // main.cpp:48: the first frame is a render()
+    if (!ckpt_in.empty()) {
+        std::ifstream f(ckpt_in, std::ios::binary);
+        char magic[4] = {0};
+        uint32_t hdr[3] = {0, 0, 0};
+        f.read(magic, 4); f.read((char*)hdr, sizeof hdr);
+        if (!f || std::memcmp(magic, "RTCK", 4) != 0 || hdr[0] != (uint32_t)W || hdr[1] != (uint32_t)H || hdr[2] == 0) {
+            std::fprintf(stderr, "cannot resume from %s (missing, damaged, or a different frame size)\n", ckpt_in.c_str());
+            return 2;
+        }
+        std::vector<float> img((size_t)W * H * 4);
+        f.read((char*)img.data(), (std::streamsize)(img.size() * 4));
+        if (!f || rt_restore_image(tracer.context(), img.data(), hdr[2]) != RT_OK) { std::fprintf(stderr, "resume failed: %s\n", rt_last_error()); return 2; }
+        camera_in_motion = false;                       // the restored image belongs to this camera: continue with renderAgain
+    }
     long frames = 0;
     const auto t0 = std::chrono::steady_clock::now();
     auto frame = [&]() {                                // main.cpp:91-95
@@ -83,6 +102,11 @@ int main(int argc, char** argv) {
     std::vector<float> img((size_t)W * H * 4);
     tracer.readImage(img.data());
     if (!out_tga.empty() && rt_write_tga(out_tga.c_str(), img.data(), W, H) != RT_OK) { std::fprintf(stderr, "%s\n", rt_last_error()); return 1; }
+    if (!ckpt_out.empty()) {
+        std::ofstream o(ckpt_out, std::ios::binary);
+        const uint32_t hdr[3] = {(uint32_t)W, (uint32_t)H, st.samples_done};
+        o.write("RTCK", 4); o.write((const char*)hdr, sizeof hdr); o.write((const char*)img.data(), (std::streamsize)(img.size() * 4));
+    }
     if (!out_raw.empty()) { std::ofstream o(out_raw, std::ios::binary); o.write((const char*)img.data(), (std::streamsize)(img.size() * 4)); }
     std::printf("{\"frames\": %ld, \"samples_in_image\": %u, \"width\": %d, \"height\": %d, \"rays\": %llu, \"seconds\": %.4f, \"mrays_per_s\": %.1f}\n",
                 frames, st.samples_done, W, H, (unsigned long long)st.rays_total, secs, st.rays_total / secs / 1e6);

@@ -70,7 +70,7 @@ def lib():
         "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
         "rt_render": [vp, vp], "rt_render_again": [vp, vp], "rt_render_samples": [vp, vp, u32, u32, u32],
         "rt_clear_accum": [vp], "rt_invalidate_caches": [vp], "rt_finalize": [vp, u32], "rt_read_image": [vp, vp], "rt_read_accum": [vp, vp],
-        "rt_read_primary_ids": [vp, vp, vp, vp], "rt_get_stats": [vp, C.POINTER(Stats)],
+        "rt_read_primary_ids": [vp, vp, vp, vp], "rt_restore_image": [vp, vp, u32], "rt_restore_accum": [vp, vp, u32], "rt_get_stats": [vp, C.POINTER(Stats)],
         "rt_accum_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_image_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
@@ -246,6 +246,16 @@ class Context:
         img = out if out is not None else np.empty((self.H, self.W, 4), dtype=np.float32)
         _check(self.L.rt_read_accum(self.h, img.ctypes.data))
         return img
+
+    def restore_image(self, img, samples):
+        a = np.ascontiguousarray(img, dtype=np.float32)
+        assert a.shape == (self.H, self.W, 4)
+        _check(self.L.rt_restore_image(self.h, a.ctypes.data, samples))
+
+    def restore_accum(self, acc, samples):
+        a = np.ascontiguousarray(acc, dtype=np.float32)
+        assert a.shape == (self.H, self.W, 4)
+        _check(self.L.rt_restore_accum(self.h, a.ctypes.data, samples))
 
     def primary_ids(self, cam):
         c = self._cam(cam)

@@ -59,3 +59,23 @@ def test_headless_script_resets_on_camera_motion(port, tmp_path):
 def test_headless_reports_scene_errors_like_the_reference(tmp_path):
     out = subprocess.run([EXE, "--scene", "bad_material.scene", "--root", ASSETS], capture_output=True, text=True, timeout=120)
     assert out.returncode != 0 and "ERROR: SCENE: MATERIAL: shiny DOES NOT EXIST" in out.stderr
+
+
+def test_headless_checkpoint_resume_is_bit_identical(tmp_path):
+    """3 samples + checkpoint, then resume + 4 more samples == 7 samples uninterrupted (the sqrt(mean) chain of
+    kernels/raytracer.cl:524-531 continues from the restored image and sample counter)."""
+    W, H = 120, 80
+    common = ["--width", str(W), "--height", str(H), "--arith", "strict", "--rng", "table", "--table-seed", "9", "--depth", "10"]
+    ck = str(tmp_path / "state.rtck")
+    a_dir, b_dir, c_dir = tmp_path / "a", tmp_path / "b", tmp_path / "c"
+    for d in (a_dir, b_dir, c_dir):
+        d.mkdir()
+    info_a, _ = run(common + ["--spp", "3", "--checkpoint", ck], a_dir)
+    assert info_a["samples_in_image"] == 3 and os.path.getsize(ck) == 16 + W * H * 16
+    info_b, raw_b = run(common + ["--spp", "4", "--resume", ck], b_dir)
+    info_c, raw_c = run(common + ["--spp", "7"], c_dir)
+    assert info_b["samples_in_image"] == 7 and info_c["samples_in_image"] == 7
+    assert np.array_equal(np.fromfile(raw_b, np.uint32), np.fromfile(raw_c, np.uint32))
+    bad = subprocess.run([EXE, "--scene", "shapes.scene", "--root", ASSETS, "--textures", ASSETS, "--width", "64", "--height", "64",
+                          "--resume", ck], capture_output=True, text=True, timeout=120)
+    assert bad.returncode == 2 and "cannot resume" in bad.stderr

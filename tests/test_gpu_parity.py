@@ -340,3 +340,27 @@ def test_fused_peer_finalize_equals_reduce_then_finalize(rt, scenes, table):
     finally:
         for c in ctxs:
             c.close()
+
+
+def test_restore_accum_and_image_continue_the_run(rt, scenes, table):
+    """rt_restore_image / rt_restore_accum (checkpoint/resume): a second context continues where the first stopped."""
+    from rtb200 import fixtures as fx
+    W, H = 96, 64
+    cam = fx.camera(60, W / H)
+    kw = dict(max_depth=30, arith=rt.ARITH_STRICT, rng_mode=rt.RNG_COUNTER_TABLE, seed=2)
+    with make_ctx(rt, scenes, "default", W, H, table, **kw) as a, make_ctx(rt, scenes, "default", W, H, table, **kw) as b:
+        a.render_samples(cam, 0, 6, rt.ACCUM_REFERENCE)
+        want = a.read_image().copy()
+        a.clear_accum(); a.render_samples(cam, 0, 6, rt.ACCUM_SUM)
+        want_acc = a.read_accum().copy()
+        a.render_samples(cam, 0, 2, rt.ACCUM_REFERENCE)
+        b.restore_image(a.read_image(), 2)
+        for _ in range(4):
+            b.render_again(cam)
+        assert b.stats().samples_done == 6 and np.array_equal(bits(b.read_image()), bits(want))
+        a.clear_accum(); a.render_samples(cam, 0, 2, rt.ACCUM_SUM)
+        b.restore_accum(a.read_accum(), 2)
+        b.render_samples(cam, 2, 4, rt.ACCUM_SUM)
+        assert b.stats().samples_done == 6 and np.array_equal(bits(b.read_accum()), bits(want_acc))
+        with pytest.raises(rt.RtError):
+            b.restore_image(want, 0)
