@@ -551,6 +551,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
     L.queries = c->d_rays + 1;
+    L.queue = reinterpret_cast<uint32_t*>(c->d_rays + 3);
     const bool use_head = c->prm.path_head == RT_HEAD_ON;
     if (!use_head && c->prm.arith == RT_ARITH_FAST) {
         int r = ensure_certified(c, cam);
@@ -558,6 +559,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
         L.certify_id = c->d_certify;
     }
     CU(cudaMemsetAsync(c->d_rays, 0, 2 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_rays + 3, 0, sizeof(unsigned long long), c->stream));
     CU(cudaEventRecord(c->ev0, c->stream));
     bool head_rebuilt = false;
     if (use_head) {

@@ -89,6 +89,8 @@ struct TraceLaunch {
     uint32_t bvh_regen;        // LBVH kernel: waiting lanes that trigger a shading/regeneration phase (0 = default 8)
     DevHead head;              // path heads of the frame (k_trace_tail_* only)
     unsigned long long* queries; // device counter: nearest-hit queries executed (k_trace_tail_*)
+    uint32_t* queue;           // device counter, zero at launch: next entry of head.list to render (k_trace_tail_*_bvh)
+    uint32_t tail_blocks;      // persistent blocks of k_trace_tail_*_bvh (set by the launcher)
 };
 
 // k_head_*: the sample-independent head of every pixel's path (see rt_kernels.cuh, "path heads").

@@ -935,42 +935,35 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 // or shade the hit and start the bounced ray; finished paths restart from the stored head.
 template <class A>
 __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
-    const uint32_t stoch_blocks = (p.head.n_stoch + kTraceThreads - 1u) / kTraceThreads;
-    if (blockIdx.x >= stoch_blocks) { terminal_body<A>(p, (blockIdx.x - stoch_blocks) * kTraceThreads + threadIdx.x); return; }
+    if (blockIdx.x >= p.tail_blocks) { terminal_body<A>(p, (blockIdx.x - p.tail_blocks) * kTraceThreads + threadIdx.x); return; }
     __shared__ float4 hs_all[4 * kTraceThreads];
     float4* hs = hs_all + threadIdx.x;
     const float4* S = p.sc.stream;
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t j = blockIdx.x * kTraceThreads + threadIdx.x;
-    const bool live = j < p.head.n_stoch;
-    const uint32_t slot = live ? __ldg(p.head.list + j) : 0u;
-    int x, y;
-    slot_pixel(slot, p.W, x, y);
-#pragma unroll
-    for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
-
-    const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
-    float4* px = p.target + (size_t)y * p.W + x;
-    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    if (live && (p.accum_mode == 1u || p.first > 0u)) acc = *px;
     const uint32_t k_end = p.first + p.n;
-    uint32_t k = live ? p.first : k_end, i, mat_id;
-    V3 o, d, out;
-    Hit h;
+    // Persistent lanes over a queue of stochastic pixels: path lengths in large scenes are heavy tailed (mirror and
+    // glass chains up to the depth limit), so with one pixel per lane most lanes of a warp idled behind its slowest
+    // pixel (ncu: 12.5 of 32 lanes traversing).  A lane renders all samples of its pixel in sample order (the
+    // accumulation order stays the reference's) and then takes the next list entry from a global counter.
+    PixelRng pr; pr.vec_base = pr.uni_base = pr.hp = 0u;
+    float4* px = nullptr;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    uint32_t k = k_end, i = 0u, mat_id = 0u;
+    V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f), out = mk(0.0f, 0.0f, 0.0f);
+    Hit h; h.t = 0.0f; h.id = kIdMiss; h.bu = h.bv = 0.0f; h.aux = 0u;
     auto restart = [&]() {
         const float4 r0 = hs[0], r1 = hs[kTraceThreads], r2 = hs[2 * kTraceThreads], r3 = hs[3 * kTraceThreads];
         o = mk(r0.x, r0.y, r0.z); d = mk(r1.x, r1.y, r1.z); out = mk(r2.x, r2.y, r2.z);
         h.t = r0.w; h.bu = r1.w; h.bv = r2.w;
         i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
     };
-    restart();
     uint32_t queries = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
     int stack[64];
     int sp = 0, node = 0;
-    bool traversing = false, has_ray = k < k_end, have_result = false;
+    bool traversing = false, has_ray = false, have_result = false, exhausted = false;
     auto start_ray = [&]() {
         h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
         hit_planes<A>(p.sc, S, o, d, h);
@@ -980,7 +973,34 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         have_result = true;
     };
 
-    while (__any_sync(RT_FULL, has_ray)) {
+    for (;;) {
+        const bool need = !exhausted && !has_ray;            // ---- lanes without a pixel: flush, take the next one
+        const unsigned nm = __ballot_sync(RT_FULL, need);
+        if (nm) {
+            if (need && px) *px = acc;
+            const int leader = __ffs((int)nm) - 1;
+            uint32_t base = 0u;
+            if ((int)lane == leader) base = atomicAdd(p.queue, (uint32_t)__popc(nm));
+            base = __shfl_sync(RT_FULL, base, leader);
+            if (need) {
+                const uint32_t j = base + (uint32_t)__popc(nm & ((1u << lane) - 1u));
+                if (j < p.head.n_stoch) {
+                    const uint32_t slot = __ldg(p.head.list + j);
+                    int x, y;
+                    slot_pixel(slot, p.W, x, y);
+#pragma unroll
+                    for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
+                    pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
+                    px = p.target + (size_t)y * p.W + x;
+                    acc = (p.accum_mode == 1u || p.first > 0u) ? *px : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    k = p.first; has_ray = true; have_result = false; traversing = false;
+                    restart();
+                } else {
+                    exhausted = true; px = nullptr;
+                }
+            }
+        }
+        if (!__any_sync(RT_FULL, has_ray)) break;
         if (has_ray && !traversing) {                        // ---- waiting lanes: close, shade, bounce, restart
             if (have_result) {
                 ++queries;
@@ -1023,11 +1043,10 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 else traversing = false;
             }
             const unsigned trav = __ballot_sync(RT_FULL, traversing);
-            const unsigned waiting = __ballot_sync(RT_FULL, has_ray && !traversing);
+            const unsigned waiting = __ballot_sync(RT_FULL, !traversing && !exhausted);   // finished a ray, or needs a pixel
             if (trav == 0u || (uint32_t)__popc(waiting) >= regen) break;
         }
     }
-    if (live) *px = acc;
     queries = __reduce_add_sync(RT_FULL, queries);
     if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
 }
@@ -1099,6 +1118,23 @@ inline size_t staged_bytes(const DevScene& sc) {
 inline size_t tail_work_items(const TraceLaunch& p) {
     const size_t T = kTraceThreads;
     return ((p.head.n_stoch + T - 1) / T + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
+}
+// k_trace_tail_*_bvh: tail_blocks persistent blocks over the queue of stochastic pixels + one block per 128 entries of
+// the rest of the list (terminal pixels)
+template <class K>
+inline cudaError_t launch_tail_bvh(K kernel, TraceLaunch p, cudaStream_t s) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceThreads, 0)) != cudaSuccess) return e;
+    const uint32_t T = kTraceThreads;
+    const uint32_t want = (p.head.n_stoch + T - 1u) / T, cap = (uint32_t)(sms * per_sm);
+    p.tail_blocks = want < cap ? want : cap;
+    const uint32_t rest_blocks = (p.head.n_slots - p.head.n_stoch + T - 1u) / T;
+    if (p.tail_blocks + rest_blocks == 0u) return cudaSuccess;
+    kernel<<<p.tail_blocks + rest_blocks, T, 0, s>>>(p);
+    return cudaGetLastError();
 }
 constexpr size_t kHeadStateBytes = 4u * kTraceThreads * sizeof(float4);   // restart state of k_trace_tail_*
 

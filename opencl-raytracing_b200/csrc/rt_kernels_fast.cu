@@ -39,7 +39,7 @@ cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_trace_fast_bvh, p, tiles * 32, s, true) : launch_staged(k_trace_fast, p, tiles * 32, s);
 }
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s) {
-    return p.bvh.n_leaves ? launch_staged(k_trace_tail_fast_bvh, p, tail_work_items(p), s, true)
+    return p.bvh.n_leaves ? launch_tail_bvh(k_trace_tail_fast_bvh, p, s)
                           : launch_staged(k_trace_tail_fast, p, tail_work_items(p), s, false, kHeadStateBytes);
 }
 cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) {

@@ -47,7 +47,7 @@ cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_head_bvh, p, p.n_slots, s, true) : launch_staged(k_head, p, p.n_slots, s);
 }
 cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s) {
-    return p.bvh.n_leaves ? launch_staged(k_trace_tail_strict_bvh, p, tail_work_items(p), s, true)
+    return p.bvh.n_leaves ? launch_tail_bvh(k_trace_tail_strict_bvh, p, s)
                           : launch_staged(k_trace_tail_strict, p, tail_work_items(p), s, false, kHeadStateBytes);
 }
 cudaError_t launch_probe_hits_strict(const ProbeLaunch& p, cudaStream_t s) {
