@@ -1,7 +1,7 @@
 // csrc/rt_bvh.cu — LBVH construction on the GPU (Lauterbach et al. 2009 / Karras 2012):
 //   k_prim_bounds   one thread per primitive: AABB (slightly inflated, conservative) + centroid
 //   cub::DeviceReduce  scene bounds of the centroids
-//   k_morton        30-bit Morton code of the centroid, extended to a unique 64-bit key (code << 32 | primitive)
+//   k_morton        63-bit Morton code of the centroid (21 bits per axis); equal codes are split by sorted position
 //   cub::DeviceRadixSort  sort keys, carrying the primitive number
 //   k_hierarchy     Karras' binary radix tree: one thread per internal node finds its range and split
 //   k_refit         one thread per leaf walks to the root; the second arrival at a node (atomic counter) merges
@@ -81,11 +81,14 @@ __global__ void k_centroid_bounds_in(const float4* c, uint32_t n, Bounds3* out) 
     out[p] = b;
 }
 
-__device__ __forceinline__ uint32_t expand10(uint32_t v) {
-    v = (v * 0x00010001u) & 0xFF0000FFu;
-    v = (v * 0x00000101u) & 0x0F00F00Fu;
-    v = (v * 0x00000011u) & 0xC30C30C3u;
-    v = (v * 0x00000005u) & 0x49249249u;
+// 21 bits -> every third bit of a 63-bit word
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
+    v &= 0x1FFFFFull;
+    v = (v | (v << 32)) & 0x1F00000000FFFFull;
+    v = (v | (v << 16)) & 0x1F0000FF0000FFull;
+    v = (v | (v << 8)) & 0x100F00F00F00F00Full;
+    v = (v | (v << 4)) & 0x10C30C30C30C30C3ull;
+    v = (v | (v << 2)) & 0x1249249249249249ull;
     return v;
 }
 __global__ void k_morton(const float4* centroids, uint32_t n, const Bounds3* scene, unsigned long long* keys, uint32_t* vals) {
@@ -93,20 +96,24 @@ __global__ void k_morton(const float4* centroids, uint32_t n, const Bounds3* sce
     if (p >= n) return;
     const Bounds3 sb = *scene;
     const float c[3] = {centroids[p].x, centroids[p].y, centroids[p].z};
-    uint32_t q[3];
+    // 63-bit codes (21 bits per axis): the scene bounds are dominated by a few huge primitives (light sphere, radius
+    // 300), so with 10 bits per axis thousands of the small triangles of a mesh shared one cell and the bottom of
+    // the tree degenerated into primitive order.
+    unsigned long long q[3];
     for (int a = 0; a < 3; ++a) {
         const float ext = fmaxf(sb.hi[a] - sb.lo[a], 1e-20f);
-        const float u = fminf(fmaxf((c[a] - sb.lo[a]) / ext, 0.0f), 1.0f);
-        q[a] = min((uint32_t)(u * 1024.0f), 1023u);
+        const double u = fmin(fmax(((double)c[a] - (double)sb.lo[a]) / (double)ext, 0.0), 1.0);
+        q[a] = (unsigned long long)fmin(u * 2097152.0, 2097151.0);
     }
-    const uint32_t code = (expand10(q[0]) << 2) | (expand10(q[1]) << 1) | expand10(q[2]);
-    keys[p] = ((unsigned long long)code << 32) | p;     // unique keys: duplicates are split by primitive number
+    keys[p] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
     vals[p] = p;
 }
 
+// common prefix of the (key, position) pairs: equal codes are told apart by their sorted position (Karras 2012 §4)
 __device__ __forceinline__ int delta(const unsigned long long* k, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
-    return __clzll((long long)(k[i] ^ k[j]));
+    const unsigned long long x = k[i] ^ k[j];
+    return x ? __clzll((long long)x) : 64 + __clz(i ^ j);
 }
 
 // Karras 2012, "Maximizing Parallelism in the Construction of BVHs, Octrees, and k-d Trees", Fig. 4.
