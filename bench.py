@@ -214,7 +214,7 @@ def main_b200(a):
         ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     from rtb200.multigpu import PeerFinalize, reduce_to_rank0, sample_range
-    peers = PeerFinalize(ctx) if fused else None
+    peers = PeerFinalize(ctx, stream_ordered=True) if fused else None
     spp = a.spp
     first, n_mine = sample_range(spp, world, rank)
 

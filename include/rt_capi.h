@@ -151,6 +151,7 @@ int rt_ipc_export(rt_ctx* ctx, void* accum_handle, void* image_handle);
 int rt_ipc_open_peers(rt_ctx* ctx, int n_ranks, int my_rank, const void* accum_handles, const void* image_handle_rank0);
 int rt_set_peers_direct(rt_ctx* ctx, int n_ranks, int my_rank, void* const* accum_ptrs, void* image_rank0);
 int rt_finalize_peers(rt_ctx* ctx, uint32_t total_spp);
+int rt_finalize_peers_async(rt_ctx* ctx, uint32_t total_spp);   /* enqueue only: ordered on the context's stream */
 int rt_close_peers(rt_ctx* ctx);
 
 /* Probes used by the parity tests: nearest hit of arbitrary rays, and one bounce of the path loop.

@@ -757,7 +757,10 @@ int rt_set_peers_direct(rt_ctx* c, int n, int rank, void* const* accum_ptrs, voi
     c->peer_n = n; c->peer_rank = rank;
     return RT_OK;
 }
-int rt_finalize_peers(rt_ctx* c, uint32_t spp) {
+static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync);
+int rt_finalize_peers(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, true); }
+int rt_finalize_peers_async(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, false); }
+static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize_peers: spp must be > 0");
     if (c->peer_n < 1) return fail(RT_ERR_STATE, "rt_finalize_peers: no peers set (rt_ipc_open_peers / rt_set_peers_direct)");
@@ -771,7 +774,7 @@ int rt_finalize_peers(rt_ctx* c, uint32_t spp) {
     P.n_pixels = (int)(px * (c->peer_rank + 1) / c->peer_n) - P.first_pixel;
     P.inv_spp = 1.0f / (float)spp;
     CU(launch_finalize_peers(P, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    if (sync) CU(cudaStreamSynchronize(c->stream));
     c->stats.kernel_launches += 1;
     return RT_OK;
 }

@@ -17,7 +17,10 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_tra
     extern __shared__ float4 smem[];
     trace_tail_body<Fused>(p, smem);
 }
-extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_fast_bvh(const __grid_constant__ TraceLaunch p) {
+#ifndef RT_BVH_MIN_BLOCKS
+#define RT_BVH_MIN_BLOCKS 8
+#endif
+extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_BVH_MIN_BLOCKS) k_trace_tail_fast_bvh(const __grid_constant__ TraceLaunch p) {
     trace_tail_bvh_body<Fused>(p);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {

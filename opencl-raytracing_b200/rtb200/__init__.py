@@ -76,7 +76,7 @@ def lib():
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
         "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
         "rt_ipc_export": [vp, vp, vp], "rt_ipc_open_peers": [vp, ci, ci, vp, vp],
-        "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_close_peers": [vp],
+        "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_finalize_peers_async": [vp, u32], "rt_close_peers": [vp],
         "rt_measure_fp32_peak": [ci, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rt_scene_load": [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)], "rt_scene_get_desc": [vp, C.POINTER(SceneDesc)],
         "rt_scene_get_textures": [vp, C.POINTER(vp), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)],
@@ -296,8 +296,8 @@ class Context:
         arr = (C.c_void_p * len(accum_ptrs))(*accum_ptrs)
         _check(self.L.rt_set_peers_direct(self.h, len(accum_ptrs), rank, arr, image_ptr_rank0))
 
-    def finalize_peers(self, spp):
-        _check(self.L.rt_finalize_peers(self.h, spp))
+    def finalize_peers(self, spp, sync=True):
+        _check((self.L.rt_finalize_peers if sync else self.L.rt_finalize_peers_async)(self.h, spp))
 
     def close_peers(self):
         _check(self.L.rt_close_peers(self.h))

@@ -33,9 +33,15 @@ class PeerFinalize:
     """Fused reduce + finalize over peer memory.  Handles are exchanged once (all_gather_object); per render every
     rank calls finalize(spp) between two barriers."""
 
-    def __init__(self, ctx, group=None):
+    def __init__(self, ctx, group=None, stream_ordered=False):
+        """stream_ordered: the context renders on torch's current CUDA stream (rt_set_stream); the two rank barriers
+        are then tiny all-reduces ordered on that stream and nothing blocks the host until the caller synchronises."""
         import torch.distributed as dist
-        self.ctx, self.group = ctx, group
+        self.ctx, self.group, self.stream_ordered = ctx, group, stream_ordered
+        self.flag = None
+        if stream_ordered:
+            import torch
+            self.flag = torch.zeros(1, dtype=torch.float32, device="cuda")
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         mine = ctx.ipc_export()
         allh = [None] * self.world
@@ -44,6 +50,11 @@ class PeerFinalize:
 
     def finalize(self, spp):
         import torch.distributed as dist
+        if self.stream_ordered:
+            dist.all_reduce(self.flag, group=self.group)      # every rank's render kernel is behind this on its stream
+            self.ctx.finalize_peers(spp, sync=False)
+            dist.all_reduce(self.flag, group=self.group)      # every slice of rank 0's image is behind this
+            return
         dist.barrier(group=self.group)       # every rank's render has finished (render calls are synchronous)
         self.ctx.finalize_peers(spp)
         dist.barrier(group=self.group)       # every slice of rank 0's image has been written
