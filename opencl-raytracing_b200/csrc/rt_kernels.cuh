@@ -64,8 +64,10 @@ __device__ __forceinline__ bool sphere_candidate(const float4 s, V3 o, V3 d, flo
     const float dis = A::msub(b, b, c);
     if (!(dis > 0.0f)) return false;
     const float sq = A::sqrt(dis);
-    t = A::sub(b, sq);
-    if (!in_range(t)) t = A::add(b, sq);
+    // near root unless it is below T_MIN; a near root beyond T_MAX makes the reference try the (still farther) far root
+    // and reject it (cl:163-171) — here the caller's t < best.t <= T_MAX test rejects it, same outcome
+    const float t0 = A::sub(b, sq), t1 = A::add(b, sq);
+    t = (t0 >= RT_T_MIN) ? t0 : t1;
     return t >= RT_T_MIN;
 }
 // cl:196-255: intersection of two balls.  Every accepted branch yields t >= T_MIN; t <= T_MAX (cl:245) is implied
@@ -283,7 +285,9 @@ __device__ __forceinline__ void hit_meshes_warp(const DevScene& sc, const float4
             const float cc = fmaf(ocx, ocx, fmaf(ocy, ocy, ocz * ocz)) - bs.w * bs.w;
             const float disc = fmaf(b, b, -a * cc);
             // 2 % slack on the entry distance: the filter must never reject a triangle that could be accepted
-            need = disc >= 0.0f && !(cc > 0.0f && b < 0.0f) && (b - sqrtf(disc)) * 0.98f - 1e-3f * a < best.t * a;
+            float sq;                                                      // approximate root: the 2 % slack covers it
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(fmaxf(disc, 0.0f)));
+            need = disc >= 0.0f && !(cc > 0.0f && b < 0.0f) && (b - sq) * 0.98f - 1e-3f * a < best.t * a;
         }
         if (!__any_sync(RT_FULL, need)) continue;
         bool open = need;

@@ -2,7 +2,7 @@
 // (FMA contraction, MUFU rcp/sqrt/rsqrt), primary hits certified against the Exact policy.
 #include "rt_kernels.cuh"
 #ifndef RT_MIN_BLOCKS
-#define RT_MIN_BLOCKS 7   // 72 registers: 28 warps per SM measured faster than 80 registers at 24 warps
+#define RT_MIN_BLOCKS 8   // 64 registers, 32 warps per SM: measured 47.3 vs 46.9 Grays/s at 7 blocks (72 registers) on C2
 #endif
 
 namespace rtb {
