@@ -17,6 +17,9 @@ struct alignas(16) BvhNode {
 };
 static_assert(sizeof(BvhNode) == 64, "one node = four 16-byte words");
 
+// One push per level of the binary tree; a Karras tree over 63-bit codes + 32-bit positions is at most 95 levels deep.
+constexpr int kBvhStack = 96;
+
 struct DevBvh {
     const BvhNode* nodes;     // n_leaves - 1 internal nodes, root = 0 (n_leaves >= 2)
     const uint2* leaves;      // per leaf slot: (hit id = kind << 28 | reference index, stream index of the primitive)

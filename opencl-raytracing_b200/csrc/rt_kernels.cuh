@@ -210,20 +210,38 @@ __device__ __forceinline__ void bvh_leaf(const DevScene& sc, const float4* __res
         }
     }
 }
+// The reference's sphere test computes dis = b*b - (oc.oc - r*r) in binary32 (cl:152-155): its absolute error grows
+// like ~12 eps |oc|^2, so from a distance D it reports hits up to sqrt(r^2 + 7e-7 D^2) - r OUTSIDE the sphere
+// (8.5e-4 D for a small sphere).  Brute force returns those hits, so a traversal that must return the same nearest hit
+// has to visit every box the ray passes within that distance: the box is inflated by kSlabSlack x (an upper bound of
+// the distance from the ray origin to its farthest corner) before the slab test.  Twelve more instructions per box;
+// RT_BVH_FAST_SLAB (fast-arithmetic render kernel only) drops the inflation.
+#define RT_SLAB_SLACK 1.0e-3f
+template <bool ROBUST>
 __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near) {
-    const float ax = (lo[0] - o.x) * inv.x, bx = (hi[0] - o.x) * inv.x;
-    const float ay = (lo[1] - o.y) * inv.y, by = (hi[1] - o.y) * inv.y;
-    const float az = (lo[2] - o.z) * inv.z, bz = (hi[2] - o.z) * inv.z;
+    float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
+    if (ROBUST) {
+        const float dl = RT_SLAB_SLACK * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
+        l0 -= dl; h0 += dl; l1 -= dl; h1 += dl; l2 -= dl; h2 += dl;
+    }
+    const float ax = l0 * inv.x, bx = h0 * inv.x;
+    const float ay = l1 * inv.y, by = h1 * inv.y;
+    const float az = l2 * inv.z, bz = h2 * inv.z;
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
     return t_near <= t_far && t_near <= t_best;
 }
+#ifdef RT_BVH_FAST_SLAB
+#define RT_RENDER_SLAB slab<A::kExact>
+#else
+#define RT_RENDER_SLAB slab<true>
+#endif
 template <class A>
 __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
     if (bvh.n_leaves == 0u) return;
     if (bvh.root < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~bvh.root)), o, d, best); return; }
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    int stack[64];
+    int stack[kBvhStack];
     int sp = 0, node = bvh.root;
     for (;;) {
         const float4* N = reinterpret_cast<const float4*>(bvh.nodes + node);
@@ -231,12 +249,12 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
         const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
-        bool h0 = slab(lo0, hi0, o, inv, best.t, t0), h1 = slab(lo1, hi1, o, inv, best.t, t1);
+        bool h0 = slab<true>(lo0, hi0, o, inv, best.t, t0), h1 = slab<true>(lo1, hi1, o, inv, best.t, t1);
         if (h0 && c0 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c0)), o, d, best); h0 = false; }
         if (h1 && c1 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c1)), o, d, best); h1 = false; }
         if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
             const bool first0 = t0 <= t1;
-            if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+            if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
             node = first0 ? c0 : c1;
         } else if (h0) node = c0;
         else if (h1) node = c1;
@@ -704,7 +722,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
 
     Hit h;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    int stack[64];
+    int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false;
     auto start_ray = [&]() {
@@ -725,12 +743,12 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
-                bool h0 = slab(lo0, hi0, o, inv, h.t, t0), h1 = slab(lo1, hi1, o, inv, h.t, t1);
+                bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
                 if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
                 if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
                 if (h0 && h1) {
                     const bool first0 = t0 <= t1;
-                    if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+                    if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
                     node = first0 ? c0 : c1;
                 } else if (h0) node = c0;
                 else if (h1) node = c1;
@@ -965,7 +983,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     uint32_t queries = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    int stack[64];
+    int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false, has_ray = false, have_result = false, exhausted = false;
     auto start_ray = [&]() {
@@ -1034,12 +1052,12 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
-                bool h0 = slab(lo0, hi0, o, inv, h.t, t0), h1 = slab(lo1, hi1, o, inv, h.t, t1);
+                bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
                 if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
                 if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
                 if (h0 && h1) {
                     const bool first0 = t0 <= t1;
-                    if (sp < 64) stack[sp++] = first0 ? c1 : c0;
+                    if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
                     node = first0 ? c0 : c1;
                 } else if (h0) node = c0;
                 else if (h1) node = c1;

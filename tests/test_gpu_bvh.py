@@ -144,3 +144,35 @@ def test_bvh_path_heads_change_nothing(arith):
         assert np.array_equal(bits(on[0]), bits(off[0])) and on[1] == off[1]
     else:
         assert abs(float((on[0][..., :3] ** 2).mean()) - float((off[0][..., :3] ** 2).mean())) < 5e-3
+
+
+def test_bvh_deep_tree_equals_brute_force():
+    """Geometrically spaced primitives give a Karras tree far deeper than log2(n) (long common Morton prefixes); the
+    traversal stack (kBvhStack) must cover it: every hit equals the brute-force kernel's."""
+    import rtb200 as rt
+    from rtb200 import synth
+    mats = synth.materials([(synth.T_DIFFUSE, (1, 1, 1), 1)])
+    n = 480
+    sph = np.zeros(n, synth.SPHERE_DT)
+    for i in range(n):
+        k, axis = i // 3, i % 3
+        x = 200.0 * (0.93 ** k)                                            # 200 ... 2e-3 along each axis in turn
+        pos = [0.0, 0.0, 0.0]
+        pos[axis] = x
+        sph[i] = ((pos[0], pos[1], pos[2] + 5.0, 0), max(0.02 * x, 4e-4), 0)
+    arrays = {"materials": synth._bytes(mats), "spheres": synth._bytes(sph), "planes": np.zeros((0, 48), np.uint8),
+              "lenses": np.zeros((0, 64), np.uint8), "vertices": np.zeros((0, 16), np.uint8), "uvs": np.zeros((0, 8), np.uint8),
+              "indices": np.zeros((0, 4), np.uint8), "meshes": np.zeros((0, 16), np.uint8), "models": np.zeros((0, 12), np.uint8)}
+    rng = np.random.RandomState(2)
+    m = 30000
+    target = np.zeros((m, 3)); ax = rng.randint(0, 3, m)
+    target[np.arange(m), ax] = 200.0 * 0.93 ** rng.uniform(0, n // 3, m)   # aim along the chains, at every scale
+    target[:, 2] += 5.0
+    o = target + rng.normal(size=(m, 3)) * np.maximum(np.abs(target).max(1, keepdims=True) * 0.5, 0.01)
+    d = target - o + rng.normal(size=(m, 3)) * 1e-3 * np.linalg.norm(target - o, axis=1, keepdims=True)
+    rays = np.concatenate([o, d / np.linalg.norm(d, axis=1, keepdims=True)], 1).astype(np.float32)
+    with ctx_for(rt, arrays, arith=rt.ARITH_STRICT, accel=rt.ACCEL_BRUTE) as b, ctx_for(rt, arrays, arith=rt.ARITH_STRICT, accel=rt.ACCEL_BVH) as v:
+        ib, tb = b.trace_rays(rays)
+        iv, tv = v.trace_rays(rays)
+    assert (ib != rt.ID_MISS).mean() > 0.1 and len(np.unique(ib)) > 100
+    assert np.array_equal(ib, iv) and np.array_equal(bits(tb), bits(tv))
