@@ -820,31 +820,45 @@ __device__ __forceinline__ void slot_pixel(uint32_t slot, int W, int& x, int& y)
 template <bool BVH>
 __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
     const float4* S = p.sc.stream;
-    if (!BVH) { stage_scene(p.sc, smem); S = smem; }
+    uint8_t* list = nullptr;
+    if (!BVH) { stage_scene(p.sc, smem); S = smem; list = warp_list(p.sc, smem); }
     const uint32_t slot = blockIdx.x * kTraceThreads + threadIdx.x;
     int x, y;
     slot_pixel(slot, p.W, x, y);
     const bool live = slot < p.n_slots && x < p.W && y < p.H;
-    unsigned long long seg = 0ull;
-    if (live) {
-        V3 o = mk(p.cam[0], p.cam[1], p.cam[2]), d = primary_dir<Exact>(p.cam, x, y, p.W, p.H), out = mk(1.0f, 1.0f, 1.0f);
-        uint32_t i = 0u, mat_id = 0u;
-        uint8_t flag = kHeadTerminal;
-        Hit h;
-        ShadeEnv env; env.sc = &p.sc; env.tex = nullptr; env.table = nullptr; env.rng_mode = 0u;
-        PixelRng pr; pr.vec_base = pr.uni_base = pr.hp = 0u;
-        for (;;) {
-            if (BVH) nearest_hit_bvh<Exact>(p.sc, S, p.bvh, o, d, h);
-            else nearest_hit_lane<Exact>(p.sc, S, o, d, p.mesh_mode, h);
+    uint32_t seg = 0u;
+    V3 o = mk(p.cam[0], p.cam[1], p.cam[2]), d = primary_dir<Exact>(p.cam, x, y, p.W, p.H), out = mk(1.0f, 1.0f, 1.0f);
+    uint32_t i = 0u, mat_id = 0u;
+    uint8_t flag = kHeadTerminal;
+    Hit h; h.t = 0.0f; h.id = kIdMiss; h.bu = h.bv = 0.0f; h.aux = 0u;
+    ShadeEnv env; env.sc = &p.sc; env.tex = nullptr; env.table = nullptr; env.rng_mode = 0u;
+    PixelRng pr; pr.vec_base = pr.uni_base = pr.hp = 0u;
+    bool walking = live;
+    while (__any_sync(RT_FULL, walking)) {                   // the warp-cooperative triangle stage needs all 32 lanes
+        Hit q;                                               // lanes that stopped keep the hit they stopped at
+        if (BVH) { if (walking) nearest_hit_bvh<Exact>(p.sc, S, p.bvh, o, d, q); }
+        else nearest_hit_warp<Exact>(p.sc, S, list, o, d, walking, p.mesh_mode, q);
+        if (walking) {
+            h = q;
             ++seg;
-            if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); break; }                       // cl:450-452
-            mat_id = hit_material(p.sc, S, h);
-            const int type = __float_as_int(__ldg(p.sc.mat + 2 * mat_id).x);
-            if (type == 5) { const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1); out = vmin(out, mk(m1.x, m1.y, m1.z)); break; }   // cl:459-462
-            if (type == 2 || type == 3 || type == 4) { flag = kHeadStochastic; break; }       // draws random numbers
-            shade<Exact>(env, S, h, mat_id, pr, o, d, out, 0u, i);                             // mirror / refractive
-            if (++i >= p.depth) break;                                                          // cl:447: loop exhausted
+            if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); walking = false; }              // cl:450-452
+            else {
+                mat_id = hit_material(p.sc, S, h);
+                const int type = __float_as_int(__ldg(p.sc.mat + 2 * mat_id).x);
+                if (type == 5) {                                                                // light, cl:459-462
+                    const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                    out = vmin(out, mk(m1.x, m1.y, m1.z));
+                    walking = false;
+                } else if (type == 2 || type == 3 || type == 4) {                               // draws random numbers
+                    flag = kHeadStochastic; walking = false;
+                } else {
+                    shade<Exact>(env, S, h, mat_id, pr, o, d, out, 0u, i);                      // mirror / refractive
+                    if (++i >= p.depth) walking = false;                                        // cl:447: loop exhausted
+                }
+            }
         }
+    }
+    if (live) {
         if (flag == kHeadStochastic) {
             p.rec[slot] = make_float4(o.x, o.y, o.z, h.t);
             p.rec[p.n_slots + slot] = make_float4(d.x, d.y, d.z, h.bu);
@@ -857,8 +871,8 @@ __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
     } else if (slot < p.n_slots) {
         p.flag[slot] = kHeadDead;
     }
-    seg = __reduce_add_sync(RT_FULL, (unsigned)seg);
-    if ((threadIdx.x & 31) == 0 && seg) atomicAdd(p.segments, seg);
+    seg = __reduce_add_sync(RT_FULL, seg);
+    if ((threadIdx.x & 31) == 0 && seg) atomicAdd(p.segments, (unsigned long long)seg);
 }
 
 // Pixels whose whole path is deterministic: every sample has the colour stored by k_head.
