@@ -53,17 +53,24 @@ static_assert(sizeof(HMaterial) == 48 && sizeof(HSphere) == 32 && sizeof(HPlane)
 template <class T>
 struct DevBuf {
     T* p = nullptr;
-    size_t n = 0;
+    size_t n = 0, cap = 0;
     ~DevBuf() { release(); }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void release() { if (p) cudaFree(p); p = nullptr; n = cap = 0; }
+    // Enqueue the copy on s (the pageable source is staged before the call returns); the allocation is reused while it
+    // is large enough.  The caller synchronises once after all uploads.
     cudaError_t upload(const std::vector<T>& v, cudaStream_t s) {
-        release();
+        const size_t want = v.size() ? v.size() : 1;
+        if (want > cap) {
+            cudaError_t e = cudaStreamSynchronize(s);      // kernels of an earlier render may still read the old array
+            if (e != cudaSuccess) return e;
+            if (p) cudaFree(p);
+            p = nullptr; cap = 0;
+            e = cudaMalloc(&p, want * sizeof(T));
+            if (e != cudaSuccess) { n = 0; return e; }
+            cap = want;
+        }
         n = v.size();
-        cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
-        if (e != cudaSuccess) return e;
-        if (n) e = cudaMemcpyAsync(p, v.data(), n * sizeof(T), cudaMemcpyHostToDevice, s);
-        if (e != cudaSuccess) return e;
-        return cudaStreamSynchronize(s);
+        return n ? cudaMemcpyAsync(p, v.data(), n * sizeof(T), cudaMemcpyHostToDevice, s) : cudaSuccess;
     }
 };
 
@@ -274,6 +281,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     CU(c->b_len_shade.upload(len_shade, s)); CU(c->b_len_mat.upload(len_mat, s));
     CU(c->b_tri_uv.upload(tri_uv, s));       CU(c->b_tri_mesh.upload(tri_mesh, s));
     CU(c->b_tri_face.upload(tri_face, s));   CU(c->b_mat.upload(mat, s));
+    CU(cudaStreamSynchronize(s));
 
     DevScene& sc = c->sc;
     sc.stream = c->b_stream.p; sc.stream_f4 = (uint32_t)stream_f4;
@@ -479,11 +487,16 @@ int rt_upload_textures(rt_ctx* c, const float* rgba, int w, int h, int layers) {
     if (w <= 0 || h <= 0 || layers <= 0) return fail(RT_ERR_INVALID, "rt_upload_textures: bad size %d x %d x %d", w, h, layers);
     Guard g(c);
     const size_t n = (size_t)w * h * layers;
-    cudaFree(c->d_tex); c->d_tex = nullptr;
-    CU(cudaMalloc(&c->d_tex, n * sizeof(float4)));
+    if (n != (size_t)c->tex.w * c->tex.h * c->tex.layers) {          // new size: allocate first, a failure keeps the old array
+        float4* fresh = nullptr;
+        CU(cudaMalloc(&fresh, n * sizeof(float4)));
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_tex);
+        c->d_tex = fresh;
+    }
+    c->tex = DevTexture{c->d_tex, w, h, layers};
     CU(cudaMemcpyAsync(c->d_tex, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->tex = DevTexture{c->d_tex, w, h, layers};
     return RT_OK;
 }
 
