@@ -112,3 +112,51 @@ def test_full_size_properties_c2(scenes, table):
     # different arithmetic -> different paths, same distribution: the difference is Monte-Carlo noise of 256 spp
     assert rms(block_means(img_fast), block_means(img_strict)) <= 0.004
     assert abs(float((img_fast[..., :3] ** 2).mean()) - float((img_strict[..., :3] ** 2).mean())) <= 1e-3
+
+
+@pytest.mark.parametrize("name,n_rays", [("c4", 800), ("c5", 4000)])
+def test_full_size_lbvh_primary_hits_equal_oracle_brute_force(port, name, n_rays):
+    """BASELINE configs C4 (1.31 M triangles + 1001 spheres) and C5 (100 001 spheres) at 3840x2160 through the GPU-built
+    LBVH: the primary hit (id and t bits) of randomly chosen pixels equals the oracle's O(N) brute force — in the strict
+    arm and, by construction (path heads are walked in Exact arithmetic), in the fast arm."""
+    import oracle_py as op
+    import rtb200 as rt
+    from rtb200 import fixtures as fx, synth
+    Wb, Hb = 3840, 2160
+    arrays, info = synth.c4_scene(subdiv=8) if name == "c4" else synth.c5_scene()
+    cam = fx.camera(60, Wb / Hb)
+    d = op.make_desc(arrays)
+    rng = np.random.RandomState(17)
+    xs, ys = rng.randint(0, Wb, n_rays), rng.randint(Hb // 3, Hb, n_rays)      # lower two thirds: where the geometry is
+    with rt.Context(Wb, Hb) as ctx:
+        ctx.set_params(max_depth=16, rng_mode=rt.RNG_COUNTER, seed=1, arith=rt.ARITH_STRICT, mesh_mode=rt.MESH_NEAREST)
+        ctx.upload_scene(arrays)
+        ids, ts = ctx.primary_ids(cam)
+        assert ctx.stats().bvh_nodes == info["spheres"] + info["triangles"] - 1
+        ctx.set_params(max_depth=16, rng_mode=rt.RNG_COUNTER, seed=1, arith=rt.ARITH_FAST, mesh_mode=rt.MESH_NEAREST)
+        ids_fast, _ = ctx.primary_ids(cam)
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, 2, rt.ACCUM_SUM)
+        acc = ctx.read_accum()
+        st = ctx.stats()
+    assert np.array_equal(ids_fast, ids)
+    assert np.all(acc[..., 3] == 2) and np.isfinite(acc).all() and st.queries_last < st.rays_last
+    llc, hor, ver = cam[3:6], cam[6:9], cam[9:12]
+    kinds = set()
+    for x, y in zip(xs, ys):
+        v = llc + np.float32(np.float32(x) / np.float32(Wb)) * hor + np.float32(np.float32(y) / np.float32(Hb)) * ver
+        # the kernels' primary direction is normalize() in the oracle's operation order; take the oracle's own
+        hit, h = port.intersect(d, cam[0:3], _normalize_like_oracle(v), op.MESH_NEAREST)
+        assert ids[y, x] == h.id, (x, y, hex(ids[y, x]), hex(h.id))
+        if hit:
+            assert np.float32(ts[y, x]).view(np.uint32) == np.float32(h.t).view(np.uint32)
+            kinds.add(h.id >> 28)
+    assert len(kinds) >= 2
+
+
+def _normalize_like_oracle(v):
+    """cl_shim / rt_oracle: normalize(v) = v * (1 / sqrt(dot(v, v))), dot = (x*x + y*y) + z*z, all binary32."""
+    f = np.float32
+    s = f(f(f(v[0] * v[0]) + f(v[1] * v[1])) + f(v[2] * v[2]))
+    inv = f(1.0) / np.sqrt(s, dtype=np.float32)
+    return np.array([v[0] * inv, v[1] * inv, v[2] * inv], np.float32)
