@@ -520,6 +520,16 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
                                       V3& o, V3& d, V3& out, uint32_t sample, uint32_t bounce) {
     const DevScene& sc = *env.sc;
     const uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
+    // issue the loads of this bounce first, so their latency overlaps the hit-point arithmetic below: the material
+    // record, and (counter-table RNG) the table entry of this (pixel, sample, bounce) — speculative, used by the
+    // diffuse / textured / dielectric branches only
+    const float4 m0 = __ldg(sc.mat + 2 * mat_id), m1 = __ldg(sc.mat + 2 * mat_id + 1);
+    uint32_t tix = 0u;
+    V3 rv_table = mk(0.0f, 0.0f, 0.0f);
+    if (env.rng_mode == 2u) {
+        tix = __umulhi(bounce_key(pr.hp, sample, bounce), RT_TABLE_N);
+        rv_table = mk(__ldg(env.table + tix), __ldg(env.table + tix + 1), __ldg(env.table + tix + 2));
+    }
     const V3 p = vmad<A>(d, h.t, o);                                // cl:141-143
     V3 n;
     uint32_t tex_id = 0u;
@@ -547,7 +557,6 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
         uvx = A::mad(uc.x, h.bv, A::mad(ub.x, h.bu, A::mul(ua.x, w)));
         uvy = A::mad(uc.y, h.bv, A::mad(ub.y, h.bu, A::mul(ua.y, w)));
     }
-    const float4 m0 = __ldg(sc.mat + 2 * mat_id), m1 = __ldg(sc.mat + 2 * mat_id + 1);
     const int type = __float_as_int(m0.x);
     const float extra = m0.y;
     V3 color = mk(m1.x, m1.y, m1.z);
@@ -557,10 +566,8 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
 
     if (type == 3 || type == 4) {                                   // diffuse / textured: rayScatter cl:393-399
         V3 rv;
-        if (env.rng_mode == 2u) {                                   // the reference's table at a counter-keyed uniform index
-            const uint32_t tix = __umulhi(bounce_hash(), RT_TABLE_N);
-            rv = mk(__ldg(env.table + tix), __ldg(env.table + tix + 1), __ldg(env.table + tix + 2));
-        } else if (env.rng_mode == 0u) rv = table_vec<A>(env.table, pr, d, s_seed);
+        if (env.rng_mode == 2u) rv = rv_table;                      // the reference's table at a counter-keyed uniform index
+        else if (env.rng_mode == 0u) rv = table_vec<A>(env.table, pr, d, s_seed);
         else rv = counter_vec<A>(bounce_hash());
         d = A::normalize(vadd<A>(n, rv));
         o = p;
@@ -587,7 +594,7 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
             float r0 = A::div(A::sub(1.0f, ratio), A::add(1.0f, ratio));   // schlick cl:401-405
             r0 = A::mul(r0, r0);
             const float prob = A::mad(A::sub(1.0f, r0), A::pow5(A::sub(1.0f, -cai)), r0);
-            const float u = (env.rng_mode == 2u) ? __ldg(env.table + 3u * RT_TABLE_N + __umulhi(bounce_hash(), RT_TABLE_N))
+            const float u = (env.rng_mode == 2u) ? __ldg(env.table + 3u * RT_TABLE_N + tix)
                           : (env.rng_mode == 0u) ? table_uniform<A>(env.table, pr, d, s_seed) : u01(draw(bounce_hash(), 0u));
             try_refract = prob < u;                                 // cl:423
         }
