@@ -159,7 +159,10 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         return fail(RT_ERR_INVALID, "null array with non-zero count");
     for (uint32_t i = 0; i < d->n_materials; ++i)
         if (mats[i].type < 0 || mats[i].type > 5) return fail(RT_ERR_INVALID, "material %u has unknown type %d", i, mats[i].type);
+    if (d->n_materials > 0x00FFFFFFu) return fail(RT_ERR_UNSUPPORTED, "more than 2^24 materials");
     auto is_textured = [&](uint32_t m) { return mats[m].type == 4; };
+    // per-primitive material word of the device arrays: index in the low 24 bits, type in the high 8 (rt_kernels.cuh)
+    auto packed = [&](uint32_t m) { return m | ((uint32_t)mats[m].type << 24); };
 
     std::vector<float4> stream, sph_shade, pla_normal, len_shade, mat;
     std::vector<uint32_t> sph_mat, pla_mat, len_mat, tri_mesh;
@@ -173,7 +176,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         if (is_textured(sph[i].mat)) return fail(RT_ERR_UNSUPPORTED, "sphere %u: textured material on a non-mesh primitive (uninitialised uv in the reference)", i);
         stream.push_back(make_float4(sph[i].pos[0], sph[i].pos[1], sph[i].pos[2], sph[i].r * sph[i].r));
         sph_shade.push_back(make_float4(sph[i].pos[0], sph[i].pos[1], sph[i].pos[2], sph[i].r));
-        sph_mat.push_back(sph[i].mat);
+        sph_mat.push_back(packed(sph[i].mat));
     }
     const uint32_t off_pla = (uint32_t)stream.size();
     for (uint32_t i = 0; i < d->n_planes; ++i) {
@@ -182,7 +185,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         stream.push_back(make_float4(pla[i].pos[0], pla[i].pos[1], pla[i].pos[2], 0.0f));
         stream.push_back(make_float4(pla[i].normal[0], pla[i].normal[1], pla[i].normal[2], 0.0f));
         pla_normal.push_back(make_float4(pla[i].normal[0], pla[i].normal[1], pla[i].normal[2], 0.0f));
-        pla_mat.push_back(pla[i].mat);
+        pla_mat.push_back(packed(pla[i].mat));
     }
     const uint32_t off_len = (uint32_t)stream.size();
     for (uint32_t i = 0; i < d->n_lenses; ++i) {
@@ -192,7 +195,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         stream.push_back(make_float4(len[i].p2[0], len[i].p2[1], len[i].p2[2], len[i].r2 * len[i].r2));
         len_shade.push_back(make_float4(len[i].p1[0], len[i].p1[1], len[i].p1[2], len[i].r1));
         len_shade.push_back(make_float4(len[i].p2[0], len[i].p2[1], len[i].p2[2], len[i].r2));
-        len_mat.push_back(len[i].mat);
+        len_mat.push_back(packed(len[i].mat));
     }
     const uint32_t off_tri = (uint32_t)stream.size();
     uint32_t n_tri = 0;
@@ -207,7 +210,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
             if (is_textured(M.mat)) max_tex = std::max<int64_t>(max_tex, me.texture_id);
             MeshInst mi{};
             mi.tri_first = n_tri; mi.tri_count = me.face_count; mi.face_id_base = me.index_anchor / 3u;
-            mi.mat_id = M.mat; mi.texture_id = me.texture_id;
+            mi.mat_id = packed(M.mat); mi.texture_id = me.texture_id;
             double cx = 0, cy = 0, cz = 0;
             std::vector<const float*> corners;
             for (uint32_t f = 0; f < me.face_count; ++f) {

@@ -503,7 +503,11 @@ __device__ __forceinline__ V3 reflect_dir(V3 d, V3 n) {            // cl:362-365
     return A::normalize(vsub<A>(d, vscale<A>(n, k)));
 }
 
-// Material of the winning primitive (cl:162, 189, 250, 314).
+// Material of the winning primitive (cl:162, 189, 250, 314) as stored per primitive by the host: material index in the
+// low 24 bits, its type (cl:23) in the high 8 — the path loop asks "is it a light?" after every query and must not
+// pay a second dependent load for that.
+__device__ __forceinline__ uint32_t mat_index(uint32_t packed) { return packed & 0x00FFFFFFu; }
+__device__ __forceinline__ int mat_type(uint32_t packed) { return (int)(packed >> 24); }
 __device__ __forceinline__ uint32_t hit_material(const DevScene& sc, const float4* __restrict__ S, const Hit& h) {
     const uint32_t kind = h.id >> 28, idx = h.id & 0x0FFFFFFFu;
     if (kind == kKindSphere) return __ldg(sc.sph_mat + idx);
@@ -523,7 +527,7 @@ __device__ __forceinline__ bool shade(const ShadeEnv& env, const float4* __restr
     // issue the loads of this bounce first, so their latency overlaps the hit-point arithmetic below: the material
     // record, and (counter-table RNG) the table entry of this (pixel, sample, bounce) — speculative, used by the
     // diffuse / textured / dielectric branches only
-    const float4 m0 = __ldg(sc.mat + 2 * mat_id), m1 = __ldg(sc.mat + 2 * mat_id + 1);
+    const float4 m0 = __ldg(sc.mat + 2 * mat_index(mat_id)), m1 = __ldg(sc.mat + 2 * mat_index(mat_id) + 1);
     uint32_t tix = 0u;
     V3 rv_table = mk(0.0f, 0.0f, 0.0f);
     if (env.rng_mode == 2u) {
@@ -851,9 +855,9 @@ __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
             if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); walking = false; }              // cl:450-452
             else {
                 mat_id = hit_material(p.sc, S, h);
-                const int type = __float_as_int(__ldg(p.sc.mat + 2 * mat_id).x);
+                const int type = mat_type(mat_id);
                 if (type == 5) {                                                                // light, cl:459-462
-                    const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                    const float4 m1 = __ldg(p.sc.mat + 2 * mat_index(mat_id) + 1);
                     out = vmin(out, mk(m1.x, m1.y, m1.z));
                     walking = false;
                 } else if (type == 2 || type == 3 || type == 4) {                               // draws random numbers
@@ -958,8 +962,8 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
                 if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }  // cl:450-452
                 else {
                     mat_id = hit_material(p.sc, S, h);
-                    if (__float_as_int(__ldg(p.sc.mat + 2 * mat_id).x) == 5) {      // light, cl:459-462
-                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                    if (mat_type(mat_id) == 5) {                                    // light, cl:459-462
+                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_index(mat_id) + 1);
                         out = vmin(out, mk(m1.x, m1.y, m1.z));
                         ended = true;
                     }
@@ -1051,8 +1055,8 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 if (h.id == kIdMiss) { out = mk(0.0f, 0.0f, 0.0f); ended = true; }      // cl:450-452
                 else {
                     mat_id = hit_material(p.sc, S, h);
-                    if (__float_as_int(__ldg(p.sc.mat + 2 * mat_id).x) == 5) {          // light, cl:459-462
-                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_id + 1);
+                    if (mat_type(mat_id) == 5) {                                        // light, cl:459-462
+                        const float4 m1 = __ldg(p.sc.mat + 2 * mat_index(mat_id) + 1);
                         out = vmin(out, mk(m1.x, m1.y, m1.z));
                         ended = true;
                     }
