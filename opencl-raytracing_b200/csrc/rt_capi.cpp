@@ -116,6 +116,9 @@ struct rt_ctx {
     float head_cam[12] = {0};
     uint32_t head_mesh_mode = 0, head_depth = 0;
     bool head_bvh = false, head_valid = false;
+    float4* d_partial = nullptr;      // chunk sums of k_trace_tail_* (TraceLaunch::partial)
+    size_t partial_cap = 0;
+    int sm_count = 0;
     // peers of the sample split (rt_ipc_open_peers / rt_set_peers_direct)
     int peer_n = 0, peer_rank = 0;
     void* peer_accum[kMaxPeers] = {nullptr};
@@ -458,7 +461,7 @@ int rt_destroy(rt_ctx* c) {
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
         rt_close_peers(c);
         cudaFree(c->d_certify);
-        cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch);
+        cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch); cudaFree(c->d_partial);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
         c->b_mat.release(); c->b_sph_mat.release(); c->b_pla_mat.release(); c->b_len_mat.release();
@@ -547,6 +550,35 @@ int rt_get_params(rt_ctx* c, rt_params* p) {
     return RT_OK;
 }
 
+// Sample chunks of the brute-force tail kernel (TraceLaunch::chunks): the fast arm's linear sums are split into items of
+// >= 16 samples until the launch has ~64 waves of blocks, so that the last wave is a few percent of the kernel and not
+// a quarter.  The strict arm keeps one item per pixel: its sums are added in sample order, like the oracle's.
+static int plan_chunks(rt_ctx* c, TraceLaunch& L) {
+    L.chunks = 1; L.chunk_spp = L.n; L.partial = nullptr;
+    if (c->prm.arith != RT_ARITH_FAST || L.accum_mode != RT_ACCUM_SUM || L.bvh.n_leaves || L.head.n_stoch == 0) return RT_OK;
+    if (!c->sm_count) {
+        int dev = 0;
+        CU(cudaGetDevice(&dev));
+        CU(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const uint64_t resident = (uint64_t)c->sm_count * 1024u, n_stoch = L.head.n_stoch;
+    uint64_t chunks = (64u * resident + n_stoch - 1u) / n_stoch;
+    if (const char* e = std::getenv("RTB200_TAIL_CHUNKS")) chunks = (uint64_t)std::atoll(e);
+    chunks = std::min<uint64_t>({chunks, L.n / 16u, (1ull << 31) / n_stoch});
+    if (chunks < 2) return RT_OK;
+    L.chunk_spp = (uint32_t)((L.n + chunks - 1u) / chunks);
+    L.chunks = (L.n + L.chunk_spp - 1u) / L.chunk_spp;
+    const size_t want = (size_t)L.chunks * n_stoch;
+    if (want > c->partial_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_partial); c->d_partial = nullptr; c->partial_cap = 0;
+        CU(cudaMalloc(&c->d_partial, want * sizeof(float4)));
+        c->partial_cap = want;
+    }
+    L.partial = c->d_partial;
+    return RT_OK;
+}
+
 static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, uint32_t accum_mode) {
     if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
     if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
@@ -583,8 +615,10 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
         if (r != RT_OK) return r;
         L.head.rec = c->d_head_rec; L.head.flag = c->d_head_flag; L.head.list = c->d_head_list;
         L.head.n_slots = c->head_n_slots; L.head.n_stoch = c->head_n_stoch;
+        { int r = plan_chunks(c, L); if (r != RT_OK) return r; }
         CU(cudaEventRecord(c->ev2, c->stream));
         CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_tail_strict(L, c->stream) : launch_trace_tail_fast(L, c->stream));
+        CU(launch_combine_chunks(L, c->stream));
     } else {
         CU(cudaEventRecord(c->ev2, c->stream));
         CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_strict(L, c->stream) : launch_trace_fast(L, c->stream));
@@ -604,7 +638,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     c->stats.rays_last = rays;
     c->stats.queries_last = use_head ? counters[1] + (head_rebuilt ? c->head_segments : 0ull) : counters[0];
     c->stats.rays_total += rays;
-    c->stats.kernel_launches += 1;
+    c->stats.kernel_launches += L.chunks > 1u ? 2 : 1;
     return RT_OK;
 }
 

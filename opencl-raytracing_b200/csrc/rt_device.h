@@ -91,6 +91,11 @@ struct TraceLaunch {
     unsigned long long* queries; // device counter: nearest-hit queries executed (k_trace_tail_*)
     uint32_t* queue;           // device counter, zero at launch: next entry of head.list to render (k_trace_tail_*_bvh)
     uint32_t tail_blocks;      // persistent blocks of k_trace_tail_*_bvh (set by the launcher)
+    // Sample chunks of k_trace_tail_* (brute-force path, linear sum): a work item is (stochastic pixel, chunk of
+    // chunk_spp samples); chunk c of list entry j leaves its sum in partial[c * n_stoch + j] and k_combine_chunks adds
+    // the chunks of a pixel in chunk order.  chunks <= 1: one item per pixel, summed straight into `target`.
+    uint32_t chunks, chunk_spp;
+    float4* partial;
 };
 
 // k_head_*: the sample-independent head of every pixel's path (see rt_kernels.cuh, "path heads").
@@ -142,6 +147,7 @@ cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s);                 // Exact arithmetic, both arms
 cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s);
+cudaError_t launch_combine_chunks(const TraceLaunch& p, cudaStream_t s);
 // list = slots partitioned by flag == kHeadStochastic (CUB DevicePartition); *n_stoch on the device
 cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s);
 cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);

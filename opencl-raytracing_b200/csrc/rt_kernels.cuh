@@ -914,9 +914,18 @@ __device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) 
 // Every lane entering a trip holds a pending hit on a surface that is neither a miss nor a light: the trip shades it,
 // traces the bounced ray, and closes the path on a miss (cl:450-452), a light (cl:459-462) or at the depth limit.  So
 // every live lane does exactly one nearest-hit query per trip; a finished path restarts from the stored head in place.
+//
+// Work items.  One lane renders all n samples of one stochastic pixel — or, when the host asks for sample chunks
+// (TraceLaunch::chunks > 1, linear sums only), chunk_spp of them: the paths of neighbouring pixels differ in length by
+// multiples (glass, mirrors facing mirrors), a block lives as long as its slowest lane, and with whole pixels as items
+// the frame is ~9 waves of blocks whose last wave leaves the SMs idle for a quarter of the kernel (ncu:
+// sm__cycles_active.avg / sm__cycles_elapsed = 0.73).  Item w = (chunk w / n_stoch, list entry w % n_stoch): a warp holds
+// neighbouring pixels of one chunk, as before.
 template <class A>
 __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* smem) {
-    const uint32_t stoch_blocks = (p.head.n_stoch + kTraceThreads - 1u) / kTraceThreads;
+    const uint32_t chunks = p.chunks > 1u ? p.chunks : 1u;
+    const uint32_t items = p.head.n_stoch * chunks;
+    const uint32_t stoch_blocks = (items + kTraceThreads - 1u) / kTraceThreads;
     if (blockIdx.x >= stoch_blocks) { terminal_body<A>(p, (blockIdx.x - stoch_blocks) * kTraceThreads + threadIdx.x); return; }
     stage_scene(p.sc, smem);
     const float4* S = smem;
@@ -924,8 +933,10 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     float4* hs = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(smem + p.sc.stream_f4 + 3u * p.sc.n_mesh + pd_f4(p.sc)) +
                                            (kTraceThreads / 32) * 1024u) + threadIdx.x;   // [4][kTraceThreads] restart state
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t j = blockIdx.x * kTraceThreads + threadIdx.x;
-    const bool live = j < p.head.n_stoch;
+    const uint32_t w = blockIdx.x * kTraceThreads + threadIdx.x;
+    const bool live = w < items;
+    const uint32_t c = live && chunks > 1u ? w / p.head.n_stoch : 0u;
+    const uint32_t j = live ? w - c * p.head.n_stoch : 0u;
     const uint32_t slot = live ? __ldg(p.head.list + j) : 0u;
     int x, y;
     slot_pixel(slot, p.W, x, y);
@@ -934,11 +945,13 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 
     const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
-    float4* px = p.target + (size_t)y * p.W + x;
+    float4* px = chunks > 1u ? p.partial + ((size_t)c * p.head.n_stoch + j) : p.target + (size_t)y * p.W + x;
     float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    if (live && (p.accum_mode == 1u || p.first > 0u)) acc = *px;
-    const uint32_t k_end = p.first + p.n;
-    uint32_t k = live ? p.first : k_end, i, mat_id;
+    if (live && chunks == 1u && (p.accum_mode == 1u || p.first > 0u)) acc = *px;
+    uint32_t k = p.first, k_end = p.first + p.n;
+    if (chunks > 1u) { k = min(k + c * p.chunk_spp, k_end); k_end = min(k + p.chunk_spp, k_end); }
+    if (!live) k = k_end;
+    uint32_t i, mat_id;
     V3 o, d, out;
     Hit h;
     auto restart = [&]() {
@@ -1163,8 +1176,8 @@ inline size_t staged_bytes(const DevScene& sc) {
 
 // grid of k_trace_tail_*: blocks of stochastic slots, then blocks over the rest of the list (terminal pixels)
 inline size_t tail_work_items(const TraceLaunch& p) {
-    const size_t T = kTraceThreads;
-    return ((p.head.n_stoch + T - 1) / T + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
+    const size_t T = kTraceThreads, items = (size_t)p.head.n_stoch * (p.chunks > 1u ? p.chunks : 1u);
+    return ((items + T - 1) / T + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
 }
 // k_trace_tail_*_bvh: tail_blocks persistent blocks over the queue of stochastic pixels + one block per 128 entries of
 // the rest of the list (terminal pixels)

@@ -40,6 +40,28 @@ cudaError_t launch_finalize_peers(const PeerFinalize& p, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// Sample chunks of k_trace_tail_* (TraceLaunch::chunks): the sums of a pixel's chunks, added to its accumulator in
+// chunk order (deterministic; 16 B per lane, the chunk planes are read coalesced).
+__global__ void __launch_bounds__(256) k_combine_chunks(const float4* __restrict__ partial, const uint32_t* __restrict__ list,
+                                                        uint32_t n_stoch, uint32_t chunks, float4* __restrict__ target, int W) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_stoch) return;
+    const uint32_t slot = list[j];
+    const int tiles_x = (W + 7) >> 3, tile = (int)(slot >> 5), lane = (int)(slot & 31u);      // slot_pixel (rt_kernels.cuh)
+    float4* px = target + (size_t)((tile / tiles_x) * 4 + (lane >> 3)) * W + (tile % tiles_x) * 8 + (lane & 7);
+    float4 a = *px;
+    for (uint32_t c = 0; c < chunks; ++c) {
+        const float4 b = partial[(size_t)c * n_stoch + j];
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    *px = a;
+}
+cudaError_t launch_combine_chunks(const TraceLaunch& p, cudaStream_t s) {
+    if (p.chunks <= 1u || p.head.n_stoch == 0u) return cudaSuccess;
+    k_combine_chunks<<<(p.head.n_stoch + 255u) / 256u, 256, 0, s>>>(p.partial, p.head.list, p.head.n_stoch, p.chunks, p.target, p.W);
+    return cudaGetLastError();
+}
+
 // Slots with a stochastic path head to the front of `list` (in slot order), all others to the back (reversed).
 struct IsStochastic {
     const uint8_t* flag;

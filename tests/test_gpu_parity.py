@@ -232,6 +232,35 @@ def test_sample_split_sums_to_whole(rt, scenes, table):
     assert np.abs(parts - whole).max() <= 1e-5 * max(1.0, float(np.abs(whole).max()))
 
 
+def test_sample_chunks_change_only_the_summation_order(rt, scenes, table, monkeypatch):
+    """The fast arm's tail kernel splits the samples of a pixel into chunks (work items small enough that the last wave
+    of blocks does not idle the SMs) and adds the chunk sums in chunk order: the paths are the same — the RNG is keyed
+    by the global sample index — so the segment and query counts are identical and the sums differ by rounding only."""
+    from rtb200 import fixtures as fx
+    W, H, spp = 320, 180, 200
+    cam = fx.camera(60, W / H)
+    res = {}
+    with make_ctx(rt, scenes, "default", W, H, table, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=9) as ctx:
+        for chunks in (1, 2, 7, 12, 0):                      # 7: ragged last chunk; 12: capped at spp / 16; 0: heuristic
+            if chunks:
+                monkeypatch.setenv("RTB200_TAIL_CHUNKS", str(chunks))
+            else:
+                monkeypatch.delenv("RTB200_TAIL_CHUNKS")
+            ctx.clear_accum()
+            ctx.render_samples(cam, 3, spp, rt.ACCUM_SUM)
+            st = ctx.stats()
+            res[chunks] = (ctx.read_accum().copy(), st.rays_last, st.queries_last)
+            ctx.render_samples(cam, 3, 40, rt.ACCUM_SUM)     # accumulates on top of what is there
+            assert np.all(ctx.read_accum()[..., 3] == spp + 40)
+    base = res[1]
+    assert base[0][..., :3].max() > 10.0
+    for chunks, (acc, rays, queries) in res.items():
+        assert np.all(acc[..., 3] == spp)
+        assert rays == base[1] and queries == base[2]
+        assert np.abs(acc - base[0]).max() <= 2e-6 * float(base[0].max()) * spp ** 0.5, chunks
+    assert not np.array_equal(res[7][0], base[0])            # the chunked path really ran
+
+
 def test_random_rays_match_oracle(rt, port, scenes, table):
     rng = np.random.RandomState(11)
     n = 20000
