@@ -135,7 +135,8 @@ static_assert(sizeof(MeshInst) == 48, "MeshInst is three 16-byte words");
 constexpr uint32_t kIdMiss = 0xFFFFFFFFu;
 constexpr uint32_t kKindSphere = 1u, kKindPlane = 2u, kKindLens = 3u, kKindTriangle = 4u;
 constexpr int kTraceThreads = 128;          // 4 warps, each an 8 x 4 pixel tile
-constexpr size_t kMaxStagedBytes = 160 * 1024;
+constexpr size_t kMaxStagedBytes = 160 * 1024;      // staged scene; the kernels add up to 8 KB of per-lane state
+constexpr size_t kMaxBlockSmemBytes = 227 * 1024;   // opt-in limit of a block on sm_100
 
 // launchers, one set per arithmetic flavour (rt_kernels_strict.cu / rt_kernels_fast.cu)
 cudaError_t launch_trace_strict(const TraceLaunch& p, cudaStream_t s);

@@ -1201,7 +1201,7 @@ constexpr size_t kHeadStateBytes = 4u * kTraceThreads * sizeof(float4);   // res
 template <class K, class P>
 inline cudaError_t launch_staged(K kernel, const P& p, size_t work_items, cudaStream_t s, bool bvh = false, size_t extra = 0) {
     const size_t smem = bvh ? 0 : staged_bytes(p.sc) + extra;
-    if (smem > kMaxStagedBytes) return cudaErrorInvalidValue;
+    if (smem > kMaxBlockSmemBytes) return cudaErrorInvalidValue;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

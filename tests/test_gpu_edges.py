@@ -134,3 +134,33 @@ def test_many_mesh_instances(port):
     arrays = mesh_scene(parts, n_spheres=10)
     got, want, st, rays_want = render_both(port, arrays, 160, 100, 4, 10, mesh_mode=0, accel=rt.ACCEL_BRUTE)
     assert int((bits(got) != bits(want)).any(-1).sum()) <= 1 and abs(int(st.rays_last) - int(rays_want)) <= 20
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+def test_largest_brute_force_scene(port, arith):
+    """Maximum size of the shared-memory path: ~9 900 spheres fill the 160 KB scene budget; the render kernels add their
+    per-lane state on top and must still launch.  Strict image == oracle; the fast arm (sample chunks) counts the same
+    number of segments per sample within Monte-Carlo noise."""
+    import rtb200 as rt
+    from rtb200 import fixtures as fx, synth
+    arrays, _ = synth.scene(n_spheres=9900, mesh_subdiv=None, seed=4, sphere_box=((-10, -5, 4), (10, 1.2, 30)), radii=(0.05, 0.15))
+    W, H, depth = 48, 24, 4
+    cam = fx.camera(60, W / H)
+    if arith == "strict":
+        got, want, st, rays_want = render_both(port, arrays, W, H, 2, depth, accel=rt.ACCEL_BRUTE)
+        assert st.bvh_nodes == 0
+        assert np.array_equal(bits(got), bits(want)) and st.rays_last == rays_want
+        return
+    with rt.Context(W, H) as ctx:
+        ctx.set_params(max_depth=depth, rng_mode=rt.RNG_COUNTER, seed=13, arith=rt.ARITH_FAST, accel=rt.ACCEL_BRUTE)
+        ctx.upload_scene(arrays)
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, 64, rt.ACCUM_SUM)
+        acc, st = ctx.read_accum(), ctx.stats()
+        assert st.bvh_nodes == 0 and np.all(acc[..., 3] == 64) and np.isfinite(acc).all()
+        ctx.set_params(max_depth=depth, rng_mode=rt.RNG_COUNTER, seed=13, arith=rt.ARITH_STRICT, accel=rt.ACCEL_BRUTE)
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, 64, rt.ACCUM_SUM)
+        ref, st_ref = ctx.read_accum(), ctx.stats()
+    assert abs(int(st.rays_last) - int(st_ref.rays_last)) <= 0.02 * st_ref.rays_last
+    assert abs(float(acc[..., :3].mean()) - float(ref[..., :3].mean())) <= 0.05 * max(1.0, float(ref[..., :3].mean()))
