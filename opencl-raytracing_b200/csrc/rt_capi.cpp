@@ -551,7 +551,7 @@ int rt_get_params(rt_ctx* c, rt_params* p) {
 }
 
 // Sample chunks of the brute-force tail kernel (TraceLaunch::chunks): the fast arm's linear sums are split into items of
-// >= 16 samples until the launch has ~64 waves of blocks, so that the last wave is a few percent of the kernel and not
+// >= 20 samples until the launch has ~64 waves of blocks, so that the last wave is a few percent of the kernel and not
 // a quarter.  The strict arm keeps one item per pixel: its sums are added in sample order, like the oracle's.
 static int plan_chunks(rt_ctx* c, TraceLaunch& L) {
     L.chunks = 1; L.chunk_spp = L.n; L.partial = nullptr;
@@ -564,7 +564,7 @@ static int plan_chunks(rt_ctx* c, TraceLaunch& L) {
     const uint64_t resident = (uint64_t)c->sm_count * 1024u, n_stoch = L.head.n_stoch;
     uint64_t chunks = (64u * resident + n_stoch - 1u) / n_stoch;
     if (const char* e = std::getenv("RTB200_TAIL_CHUNKS")) chunks = (uint64_t)std::atoll(e);
-    chunks = std::min<uint64_t>({chunks, L.n / 16u, (1ull << 31) / n_stoch});
+    chunks = std::min<uint64_t>({chunks, L.n / 20u, (1ull << 31) / n_stoch});
     if (chunks < 2) return RT_OK;
     L.chunk_spp = (uint32_t)((L.n + chunks - 1u) / chunks);
     L.chunks = (L.n + L.chunk_spp - 1u) / L.chunk_spp;

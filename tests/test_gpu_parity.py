@@ -242,7 +242,7 @@ def test_sample_chunks_change_only_the_summation_order(rt, scenes, table, monkey
     res = {}
     with make_ctx(rt, scenes, "default", W, H, table, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=9) as ctx:
         ctx.render_samples(cam, 0, 1, rt.ACCUM_SUM)           # builds the path heads (their queries count once)
-        for chunks in (1, 2, 7, 12, 0):                      # 7: ragged last chunk; 12: capped at spp / 16; 0: heuristic
+        for chunks in (1, 2, 7, 12, 0):                      # 7: ragged last chunk; 12: capped at spp / 20; 0: heuristic
             if chunks:
                 monkeypatch.setenv("RTB200_TAIL_CHUNKS", str(chunks))
             else:
