@@ -166,10 +166,18 @@ __global__ void k_refit(int n, const int2* children, const int* parent, const ui
     }
 }
 
-__global__ void k_emit_nodes(int n, const int2* children, const uint32_t* sorted, const Box* prim_box, const Box* node_box,
-                             const uint2* leaf_info, BvhNode* nodes, uint2* leaves) {
+__global__ void k_emit_nodes(BvhBuildInput in, int n, const int2* children, const uint32_t* sorted, const Box* prim_box, const Box* node_box,
+                             const uint2* leaf_info, BvhNode* nodes, float4* leaves) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) leaves[i] = leaf_info[sorted[i]];
+    if (i < n) {                                        // leaf record: the primitive's words of the stream + its ids
+        const uint2 info = leaf_info[sorted[i]];
+        const uint32_t kind = info.x >> 28;
+        const float4* src = in.stream + (kind == 1u ? info.y : kind == 3u ? in.off_len + 2u * info.y : in.off_tri + 3u * info.y);
+        const uint32_t words = kind == 1u ? 1u : kind == 3u ? 2u : 3u;
+        const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (uint32_t w = 0; w < 3u; ++w) leaves[4 * (size_t)i + w] = w < words ? src[w] : zero;
+        leaves[4 * (size_t)i + 3] = make_float4(__uint_as_float(info.x), __uint_as_float(info.y), 0.0f, 0.0f);
+    }
     if (i >= n - 1) return;
     const int2 ch = children[i];
     const Box a = child_box(ch.x, node_box, prim_box, sorted), b = child_box(ch.y, node_box, prim_box, sorted);
@@ -214,7 +222,7 @@ cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t st
     unsigned int* visits = nullptr;
     BV(tmp.get(&prim_box, n)); BV(tmp.get(&centroids, n)); BV(tmp.get(&leaf_info, n)); BV(tmp.get(&cb, n)); BV(tmp.get(&scene, 1));
     BV(tmp.get(&keys, n)); BV(tmp.get(&keys_sorted, n)); BV(tmp.get(&vals, n)); BV(tmp.get(&sorted, n));
-    BV(cudaMalloc(&out.leaves, (size_t)n * sizeof(uint2)));
+    BV(cudaMalloc(&out.leaves, (size_t)n * 4 * sizeof(float4)));
     BV(cudaMalloc(&out.nodes, (size_t)(n > 1 ? n - 1 : 1) * sizeof(BvhNode)));
     out.n_leaves = n;
 
@@ -234,7 +242,7 @@ cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t st
     BV(tmp.get((char**)&sscratch, sbytes));
     BV(cub::DeviceRadixSort::SortPairs(sscratch, sbytes, keys, keys_sorted, vals, sorted, (int)n, 0, 64, st));
     if (n == 1) {
-        k_emit_nodes<<<1, 32, 0, st>>>(1, nullptr, sorted, prim_box, nullptr, leaf_info, out.nodes, out.leaves);
+        k_emit_nodes<<<1, 32, 0, st>>>(in, 1, nullptr, sorted, prim_box, nullptr, leaf_info, out.nodes, out.leaves);
         BV(cudaGetLastError());
         return cudaStreamSynchronize(st);
     }
@@ -242,7 +250,7 @@ cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t st
     BV(cudaMemsetAsync(visits, 0, (size_t)(n - 1) * sizeof(unsigned int), st));
     k_hierarchy<<<G, T, 0, st>>>(keys_sorted, (int)n, children, parent);
     k_refit<<<G, T, 0, st>>>((int)n, children, parent, sorted, prim_box, node_box, visits);
-    k_emit_nodes<<<G, T, 0, st>>>((int)n, children, sorted, prim_box, node_box, leaf_info, out.nodes, out.leaves);
+    k_emit_nodes<<<G, T, 0, st>>>(in, (int)n, children, sorted, prim_box, node_box, leaf_info, out.nodes, out.leaves);
     BV(cudaGetLastError());
     return cudaStreamSynchronize(st);
 }

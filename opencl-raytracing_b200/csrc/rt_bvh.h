@@ -22,7 +22,8 @@ constexpr int kBvhStack = 96;
 
 struct DevBvh {
     const BvhNode* nodes;     // n_leaves - 1 internal nodes, root = 0 (n_leaves >= 2)
-    const uint2* leaves;      // per leaf slot: (hit id = kind << 28 | reference index, stream index of the primitive)
+    const float4* leaves;     // per leaf slot (Morton order) 4 x float4: the primitive's test data as in the stream (sphere: 1,
+                              // lens: 2, triangle: 3 words), then (hit id = kind << 28 | reference index, stream index, 0, 0)
     uint32_t n_leaves;        // 0 = no BVH (brute-force path)
     int32_t root;             // 0, or ~0 when the tree is a single leaf
 };
@@ -36,7 +37,7 @@ struct BvhBuildInput {        // device pointers into the scene buffers
 
 struct BvhBuffers {           // owned by the context; (re)allocated by build_lbvh
     BvhNode* nodes = nullptr;
-    uint2* leaves = nullptr;
+    float4* leaves = nullptr;
     uint32_t n_leaves = 0;
 };
 

@@ -123,8 +123,7 @@ __device__ __forceinline__ void hit_analytic(const DevScene& sc, const float4* _
 
 // cl:257-289 Moller-Trumbore on one triangle of the stream, WITHOUT the front-face test (done by the caller).
 template <class A>
-__device__ __forceinline__ bool hit_triangle(const float4* __restrict__ T, V3 o, V3 d, float& t, float& u, float& v) {
-    const float4 q0 = T[0], q1 = T[1], q2 = T[2];
+__device__ __forceinline__ bool hit_triangle(const float4 q0, const float4 q1, const float4 q2, V3 o, V3 d, float& t, float& u, float& v) {
     const V3 e1 = mk(q0.w, q1.x, q1.y), e2 = mk(q1.z, q1.w, q2.x);
     const V3 h = cross<A>(d, e2);
     const float a = dot<A>(e1, h);
@@ -138,6 +137,10 @@ __device__ __forceinline__ bool hit_triangle(const float4* __restrict__ T, V3 o,
     if (v < 0.0f || A::add(u, v) > 1.0f) return false;
     t = A::mul(f, dot<A>(e2, qv));
     return in_range(t);
+}
+template <class A>
+__device__ __forceinline__ bool hit_triangle(const float4* __restrict__ T, V3 o, V3 d, float& t, float& u, float& v) {
+    return hit_triangle<A>(T[0], T[1], T[2], o, d, t, u, v);
 }
 template <class A>
 __device__ __forceinline__ bool front_facing(const float4* __restrict__ T, V3 d) {   // cl:285,295
@@ -191,22 +194,23 @@ static __device__ __noinline__ Hit nearest_hit_exact_cold(const DevScene& sc, co
 __device__ __forceinline__ bool closer(float t, uint32_t id, const Hit& best) {
     return t < best.t || (t == best.t && t < RT_T_MAX && id < best.id);
 }
+// One leaf = one primitive; its 64-byte record (DevBvh::leaves, leaf order = Morton order) holds the test data of the
+// primitive itself, so a leaf visit is one fetch of two sectors next to those of the neighbouring leaves, not an
+// index followed by a dependent fetch from the scene's stream.
 template <class A>
-__device__ __forceinline__ void bvh_leaf(const DevScene& sc, const float4* __restrict__ S, const uint2 lf, V3 o, V3 d, Hit& best) {
-    const uint32_t kind = lf.x >> 28;
+__device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 d, Hit& best) {
+    const float4 r0 = __ldg(L), r1 = __ldg(L + 1), r2 = __ldg(L + 2), r3 = __ldg(L + 3);
+    const uint32_t id = __float_as_uint(r3.x), idx = __float_as_uint(r3.y), kind = id >> 28;
     if (kind == kKindSphere) {
         float t;
-        if (sphere_candidate<A>(__ldg(S + lf.y), o, d, t) && closer(t, lf.x, best)) { best.t = t; best.id = lf.x; best.aux = 0u; }
+        if (sphere_candidate<A>(r0, o, d, t) && closer(t, id, best)) { best.t = t; best.id = id; best.aux = 0u; }
     } else if (kind == kKindLens) {
         float t; uint32_t side;
-        if (lens_candidate<A>(__ldg(S + sc.off_len + 2 * lf.y), __ldg(S + sc.off_len + 2 * lf.y + 1), o, d, t, side) && closer(t, lf.x, best)) {
-            best.t = t; best.id = lf.x; best.aux = side;
-        }
+        if (lens_candidate<A>(r0, r1, o, d, t, side) && closer(t, id, best)) { best.t = t; best.id = id; best.aux = side; }
     } else {
-        const float4* T = S + sc.off_tri + 3 * lf.y;
         float t, u, v;
-        if (front_facing<A>(T, d) && hit_triangle<A>(T, o, d, t, u, v) && closer(t, lf.x, best)) {
-            best.t = t; best.id = lf.x; best.bu = u; best.bv = v; best.aux = lf.y;
+        if (dot<A>(mk(r2.y, r2.z, r2.w), d) < 0.0f && hit_triangle<A>(r0, r1, r2, o, d, t, u, v) && closer(t, id, best)) {   // cl:285,295
+            best.t = t; best.id = id; best.bu = u; best.bv = v; best.aux = idx;
         }
     }
 }
@@ -239,7 +243,7 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
 template <class A>
 __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
     if (bvh.n_leaves == 0u) return;
-    if (bvh.root < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~bvh.root)), o, d, best); return; }
+    if (bvh.root < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~bvh.root), o, d, best); return; }
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     int stack[kBvhStack];
     int sp = 0, node = bvh.root;
@@ -250,8 +254,8 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
         bool h0 = slab<true>(lo0, hi0, o, inv, best.t, t0), h1 = slab<true>(lo1, hi1, o, inv, best.t, t1);
-        if (h0 && c0 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c0)), o, d, best); h0 = false; }
-        if (h1 && c1 < 0) { bvh_leaf<A>(sc, S, __ldg(bvh.leaves + (~c1)), o, d, best); h1 = false; }
+        if (h0 && c0 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c0), o, d, best); h0 = false; }
+        if (h1 && c1 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c1), o, d, best); h1 = false; }
         if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
             const bool first0 = t0 <= t1;
             if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
@@ -740,7 +744,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
         h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
         hit_planes<A>(p.sc, S, o, d, h);
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
-        if (traversing && node < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~node)), o, d, h); traversing = false; }
+        if (traversing && node < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~node), o, d, h); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     };
     bool has_ray = k < k_end;
@@ -755,8 +759,8 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
                 bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
-                if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
-                if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
+                if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
+                if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
                 if (h0 && h1) {
                     const bool first0 = t0 <= t1;
                     if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
@@ -1028,7 +1032,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
         hit_planes<A>(p.sc, S, o, d, h);
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
-        if (traversing && node < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~node)), o, d, h); traversing = false; }
+        if (traversing && node < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~node), o, d, h); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
         have_result = true;
     };
@@ -1091,8 +1095,8 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
                 bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
-                if (h0 && c0 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c0)), o, d, h); h0 = false; }
-                if (h1 && c1 < 0) { bvh_leaf<A>(p.sc, S, __ldg(p.bvh.leaves + (~c1)), o, d, h); h1 = false; }
+                if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
+                if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
                 if (h0 && h1) {
                     const bool first0 = t0 <= t1;
                     if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
