@@ -134,7 +134,10 @@ static_assert(sizeof(MeshInst) == 48, "MeshInst is three 16-byte words");
 
 constexpr uint32_t kIdMiss = 0xFFFFFFFFu;
 constexpr uint32_t kKindSphere = 1u, kKindPlane = 2u, kKindLens = 3u, kKindTriangle = 4u;
-constexpr int kTraceThreads = 128;          // 4 warps, each an 8 x 4 pixel tile
+#ifndef RT_TRACE_THREADS
+#define RT_TRACE_THREADS 128
+#endif
+constexpr int kTraceThreads = RT_TRACE_THREADS;          // 4 warps, each an 8 x 4 pixel tile
 constexpr size_t kMaxStagedBytes = 160 * 1024;      // staged scene; the kernels add up to 8 KB of per-lane state
 constexpr size_t kMaxBlockSmemBytes = 227 * 1024;   // opt-in limit of a block on sm_100
 
