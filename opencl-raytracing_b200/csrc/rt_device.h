@@ -96,6 +96,12 @@ struct TraceLaunch {
     // the chunks of a pixel in chunk order.  chunks <= 1: one item per pixel, summed straight into `target`.
     uint32_t chunks, chunk_spp;
     float4* partial;
+    // Longest blocks first (k_trace_tail_*, brute-force path).  A "pixel block" is kTraceThreads consecutive entries of
+    // the stochastic list; block_cost[pb] (written when non-null) = queries the block executed; block_order (when
+    // non-null) = pixel blocks by decreasing cost: block i of the grid renders chunk i % chunks of pixel block
+    // block_order[i / chunks] instead of the blocks in list order.
+    uint32_t* block_cost;
+    const uint32_t* block_order;
 };
 
 // k_head_*: the sample-independent head of every pixel's path (see rt_kernels.cuh, "path heads").
@@ -152,6 +158,8 @@ cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s);                 //
 cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_combine_chunks(const TraceLaunch& p, cudaStream_t s);
+cudaError_t sort_blocks_by_cost(const uint32_t* cost, uint32_t* cost_sorted, uint32_t* iota, uint32_t* order, uint32_t n,
+                                void* scratch, size_t& scratch_bytes, cudaStream_t s);
 // list = slots partitioned by flag == kHeadStochastic (CUB DevicePartition); *n_stoch on the device
 cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s);
 cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);

@@ -928,8 +928,8 @@ __device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) 
 template <class A>
 __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* smem) {
     const uint32_t chunks = p.chunks > 1u ? p.chunks : 1u;
-    const uint32_t items = p.head.n_stoch * chunks;
-    const uint32_t stoch_blocks = (items + kTraceThreads - 1u) / kTraceThreads;
+    const uint32_t pixel_blocks = (p.head.n_stoch + kTraceThreads - 1u) / kTraceThreads;
+    const uint32_t stoch_blocks = pixel_blocks * chunks;
     if (blockIdx.x >= stoch_blocks) { terminal_body<A>(p, (blockIdx.x - stoch_blocks) * kTraceThreads + threadIdx.x); return; }
     stage_scene(p.sc, smem);
     const float4* S = smem;
@@ -937,10 +937,12 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     float4* hs = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(smem + p.sc.stream_f4 + 3u * p.sc.n_mesh + pd_f4(p.sc)) +
                                            (kTraceThreads / 32) * 1024u) + threadIdx.x;   // [4][kTraceThreads] restart state
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t w = blockIdx.x * kTraceThreads + threadIdx.x;
-    const bool live = w < items;
-    const uint32_t c = live && chunks > 1u ? w / p.head.n_stoch : 0u;
-    const uint32_t j = live ? w - c * p.head.n_stoch : 0u;
+    // block -> (chunk c, pixel block pb): list order, or the most expensive pixel blocks first (TraceLaunch::block_order)
+    uint32_t c, pb;
+    if (p.block_order) { c = blockIdx.x % chunks; pb = __ldg(p.block_order + blockIdx.x / chunks); }
+    else { c = blockIdx.x / pixel_blocks; pb = blockIdx.x - c * pixel_blocks; }
+    const uint32_t j = pb * kTraceThreads + threadIdx.x;
+    const bool live = j < p.head.n_stoch;
     const uint32_t slot = live ? __ldg(p.head.list + j) : 0u;
     int x, y;
     slot_pixel(slot, p.W, x, y);
@@ -991,7 +993,10 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     }
     if (live) *px = acc;
     queries = __reduce_add_sync(RT_FULL, queries);                                   // < 2^32 per warp launch
-    if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
+    if (lane == 0u && queries) {
+        atomicAdd(p.queries, (unsigned long long)queries);
+        if (p.block_cost) atomicAdd(p.block_cost + pb, queries);
+    }
 }
 
 // LBVH flavour of trace_tail_body: lanes advance ONE node per trip of the traversal loop (see trace_body_bvh); a lane
@@ -1180,8 +1185,8 @@ inline size_t staged_bytes(const DevScene& sc) {
 
 // grid of k_trace_tail_*: blocks of stochastic slots, then blocks over the rest of the list (terminal pixels)
 inline size_t tail_work_items(const TraceLaunch& p) {
-    const size_t T = kTraceThreads, items = (size_t)p.head.n_stoch * (p.chunks > 1u ? p.chunks : 1u);
-    return ((items + T - 1) / T + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
+    const size_t T = kTraceThreads, blocks = ((size_t)p.head.n_stoch + T - 1) / T * (p.chunks > 1u ? p.chunks : 1u);
+    return (blocks + (p.head.n_slots - p.head.n_stoch + T - 1) / T) * T;
 }
 // k_trace_tail_*_bvh: tail_blocks persistent blocks over the queue of stochastic pixels + one block per 128 entries of
 // the rest of the list (terminal pixels)

@@ -62,6 +62,21 @@ cudaError_t launch_combine_chunks(const TraceLaunch& p, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// Pixel blocks by decreasing cost (TraceLaunch::block_order): scratch == nullptr returns the scratch size.
+__global__ void k_iota(uint32_t* v, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
+}
+cudaError_t sort_blocks_by_cost(const uint32_t* cost, uint32_t* cost_sorted, uint32_t* iota, uint32_t* order, uint32_t n,
+                                void* scratch, size_t& scratch_bytes, cudaStream_t s) {
+    if (scratch && n) {
+        k_iota<<<(n + 255u) / 256u, 256, 0, s>>>(iota, n);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cub::DeviceRadixSort::SortPairsDescending(scratch, scratch_bytes, cost, cost_sorted, iota, order, (int)n, 0, 32, s);
+}
+
 // Slots with a stochastic path head to the front of `list` (in slot order), all others to the back (reversed).
 struct IsStochastic {
     const uint8_t* flag;
