@@ -920,11 +920,11 @@ __device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) 
 // every live lane does exactly one nearest-hit query per trip; a finished path restarts from the stored head in place.
 //
 // Work items.  One lane renders all n samples of one stochastic pixel — or, when the host asks for sample chunks
-// (TraceLaunch::chunks > 1, linear sums only), chunk_spp of them: the paths of neighbouring pixels differ in length by
-// multiples (glass, mirrors facing mirrors), a block lives as long as its slowest lane, and with whole pixels as items
-// the frame is ~9 waves of blocks whose last wave leaves the SMs idle for a quarter of the kernel (ncu:
-// sm__cycles_active.avg / sm__cycles_elapsed = 0.73).  Item w = (chunk w / n_stoch, list entry w % n_stoch): a warp holds
-// neighbouring pixels of one chunk, as before.
+// (TraceLaunch::chunks > 1, linear sums only), chunk_spp of them.  Grid block -> (chunk, block of kTraceThreads
+// consecutive list entries), in list order or with the most expensive pixel blocks first (TraceLaunch::block_order): the
+// paths of neighbouring image regions differ in length by multiples (glass, mirrors facing mirrors), a block lives as
+// long as its slowest lane, and in list order the late, expensive blocks left the SMs idle for a quarter of the kernel
+// (ncu: sm__cycles_active.avg / sm__cycles_elapsed = 0.73).  See order_blocks / plan_chunks in rt_capi.cpp.
 template <class A>
 __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* smem) {
     const uint32_t chunks = p.chunks > 1u ? p.chunks : 1u;
