@@ -2,7 +2,7 @@
 // (FMA contraction, MUFU rcp/sqrt/rsqrt), primary hits certified against the Exact policy.
 #include "rt_kernels.cuh"
 #ifndef RT_MIN_BLOCKS
-#define RT_MIN_BLOCKS 8   // 64 registers, 32 warps per SM: measured 47.3 vs 46.9 Grays/s at 7 blocks (72 registers) on C2
+#define RT_MIN_BLOCKS 7   // 71 registers, no spills, 28 warps per SM: 69.5 vs 68.6 Grays/s at 8 blocks (64 registers, 24 B of spills) on C2
 #endif
 
 namespace rtb {
