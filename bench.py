@@ -31,6 +31,15 @@ METRIC = "Mrays/s at 1080p per scene, 1/2/4/8 B200, vs reference OpenCL on host 
 WORKLOAD = "C2: default scene (8 spheres, 1 plane, 1 lens, 2 textured cubes = 24 triangles), 1920x1080, 1024 spp, max depth 30"
 
 
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write banners to fd 1 (NCCL prints its version there when the
+    box sets NCCL_DEBUG), so fd 1 is pointed at stderr for the whole run and the line goes to the saved descriptor."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -180,7 +189,7 @@ def main_reference(a):
         "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": round(rate, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0}), file=JSON_OUT, flush=True)
 
 
 def main_b200(a):
@@ -363,13 +372,14 @@ def main_b200(a):
             out["cpu_baseline"] = {"value": round(rate, 3), "unit": "Mrays/s", "cores": cores, "kind": kind,
                                    "sample": "%dx%d, 128 timed spp in 4 steps (one pass per sample), depth %d, %.1f s of CPU work"
                                              % (W, H, DEPTH, secs)}
-        print(json.dumps(out))
+        print(json.dumps(out), file=JSON_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     args = parse()
+    JSON_OUT = claim_stdout()
     select_config(args)
     if args.impl == "reference":
         main_reference(args)

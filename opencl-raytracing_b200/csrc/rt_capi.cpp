@@ -272,7 +272,6 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
     }
     while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
-    while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
     c->staged_bytes = (stream.size() + 3 * inst.size() + tri_pd.size() / 4) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
     c->n_finite = d->n_spheres + d->n_lenses + n_tri;
     if (c->prm.accel == RT_ACCEL_BRUTE && c->staged_bytes > kMaxStagedBytes)
