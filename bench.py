@@ -351,9 +351,9 @@ def main_b200(a):
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32_issue", "achieved": round(achieved, 1), "peak": round(peak_gslots, 1),
                          "unit": "G lane-slots/s", "frac": round(achieved / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
-                         "traffic": (161919232 if (CONFIG == "c2" and spp == 1024 and world == 1 and not a.no_heads and a.arith == "fast") else None),
+                         "traffic": (161039360 if (CONFIG == "c2" and spp == 1024 and world == 1 and not a.no_heads and a.arith == "fast") else None),
                          "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one k_trace_tail_fast launch of this command, bytes, from "
-                                         "profiles/r01_v7_k_trace_tail_fast_ncu_summary.txt (ncu --set full); null for other configurations",
+                                         "profiles/r01_v7b_k_trace_tail_fast_ncu_summary.txt (ncu --set full, the final round-1 build); null for other configurations",
                          "kernel": kernel, "kernel_ms": round(k_ms, 3),
                          "achieved_executed": round(executed, 1),
                          "frac_executed": round(executed / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
