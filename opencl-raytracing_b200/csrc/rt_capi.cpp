@@ -9,6 +9,7 @@
 #include "rt_device.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -16,6 +17,7 @@
 #include <cstring>
 #include <random>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace rtb;
@@ -58,8 +60,9 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; n = cap = 0; }
     // Enqueue the copy on s (the pageable source is staged before the call returns); the allocation is reused while it
     // is large enough.  The caller synchronises once after all uploads.
-    cudaError_t upload(const std::vector<T>& v, cudaStream_t s) {
-        const size_t want = v.size() ? v.size() : 1;
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t s) { return upload(v.data(), v.size(), s); }
+    cudaError_t upload(const T* src, size_t count, cudaStream_t s) {
+        const size_t want = count ? count : 1;
         if (want > cap) {
             cudaError_t e = cudaStreamSynchronize(s);      // kernels of an earlier render may still read the old array
             if (e != cudaSuccess) return e;
@@ -69,8 +72,8 @@ struct DevBuf {
             if (e != cudaSuccess) { n = 0; return e; }
             cap = want;
         }
-        n = v.size();
-        return n ? cudaMemcpyAsync(p, v.data(), n * sizeof(T), cudaMemcpyHostToDevice, s) : cudaSuccess;
+        n = count;
+        return n ? cudaMemcpyAsync(p, src, n * sizeof(T), cudaMemcpyHostToDevice, s) : cudaSuccess;
     }
 };
 
@@ -94,6 +97,8 @@ struct rt_ctx {
     DevBuf<float2> b_tri_uv;
     DevBuf<uint32_t> b_tri_face;      // reference-global face number per stream triangle (BVH leaf ids)
     BvhBuffers bvh;                   // GPU-built LBVH (empty while the brute-force path is active)
+    void* h_stage = nullptr;          // pinned host staging of the per-triangle arrays (grow-only), see convert_scene
+    size_t h_stage_cap = 0;
     size_t staged_bytes = 0;          // shared memory the brute-force path needs for this scene
     uint32_t n_finite = 0;            // spheres + lenses + triangles
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO, RT_HEAD_ON};
@@ -174,10 +179,7 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     auto packed = [&](uint32_t m) { return m | ((uint32_t)mats[m].type << 24); };
 
     std::vector<float4> stream, sph_shade, pla_normal, len_shade, mat;
-    std::vector<uint32_t> sph_mat, pla_mat, len_mat, tri_mesh;
-    std::vector<float2> tri_uv;
-    std::vector<float> tri_pd;
-    std::vector<uint32_t> tri_face;
+    std::vector<uint32_t> sph_mat, pla_mat, len_mat;
     std::vector<MeshInst> inst;
 
     for (uint32_t i = 0; i < d->n_spheres; ++i) {
@@ -209,6 +211,9 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
     const uint32_t off_tri = (uint32_t)stream.size();
     uint32_t n_tri = 0;
     int64_t max_tex = -1;
+    // pass 1: validate the model / mesh tables, lay the mesh instances out in hitModel order
+    struct Src { uint32_t vertex_anchor, index_anchor, mesh; };
+    std::vector<Src> src;
     for (uint32_t mo = 0; mo < d->n_models; ++mo) {
         const HModel& M = models[mo];
         if (M.mat >= d->n_materials) return fail(RT_ERR_INVALID, "ERROR: MATERIAL OF ID: %u DOES NOT EXIST", M.mat);
@@ -216,21 +221,65 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         for (uint32_t k = 0; k < M.mesh_count; ++k) {
             const HMesh& me = meshes[M.mesh_anchor + k];
             if ((uint64_t)me.index_anchor + 3ull * me.face_count > d->n_indices) return fail(RT_ERR_INVALID, "mesh %u: index range out of bounds", M.mesh_anchor + k);
+            if ((uint64_t)n_tri + me.face_count > 0x0FFFFFFFull) return fail(RT_ERR_UNSUPPORTED, "more than 2^28 triangles");
             if (is_textured(M.mat)) max_tex = std::max<int64_t>(max_tex, me.texture_id);
             MeshInst mi{};
             mi.tri_first = n_tri; mi.tri_count = me.face_count; mi.face_id_base = me.index_anchor / 3u;
             mi.mat_id = packed(M.mat); mi.texture_id = me.texture_id;
+            inst.push_back(mi);
+            src.push_back(Src{me.vertex_anchor, me.index_anchor, M.mesh_anchor + k});
+            n_tri += me.face_count;
+        }
+    }
+    // pass 2: the per-triangle records, written in place; long meshes are split over the host threads (a 1.3 M-triangle
+    // mesh took 0.6 s on one core, which is what an upload-per-frame caller of a large scene waits for)
+    // They go straight into pinned host memory owned by the context (no page faults or zero fill per upload, and the
+    // copies to the device run at PCIe speed), laid out as the device wants it:
+    // all = [test stream | mesh-instance table (3 x 16 B each) | plane offsets (padded to x4)], then uv, mesh, face id.
+    const size_t stream_f4 = (size_t)off_tri + 3u * (size_t)n_tri, pd_n = ((size_t)n_tri + 3u) / 4u;
+    const size_t all_f4 = stream_f4 + 3u * inst.size() + pd_n;
+    auto up16 = [](size_t b) { return (b + 15u) & ~(size_t)15u; };
+    const size_t b_all = all_f4 * sizeof(float4), b_uv = up16(3u * (size_t)n_tri * sizeof(float2)), b_u32 = up16((size_t)n_tri * sizeof(uint32_t));
+    const size_t b_total = b_all + b_uv + 2u * b_u32 + 16u;
+    CU(cudaStreamSynchronize(c->stream));                     // nothing may still read the staging area or the old arrays
+    if (b_total > c->h_stage_cap) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->h_stage_cap = 0;
+        CU(cudaMallocHost(&c->h_stage, b_total));
+        c->h_stage_cap = b_total;
+    }
+    float4* all = static_cast<float4*>(c->h_stage);
+    float2* tri_uv = reinterpret_cast<float2*>(static_cast<uint8_t*>(c->h_stage) + b_all);
+    uint32_t* tri_mesh = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->h_stage) + b_all + b_uv);
+    uint32_t* tri_face = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->h_stage) + b_all + b_uv + b_u32);
+    float* tri_pd = reinterpret_cast<float*>(all + stream_f4 + 3u * inst.size());
+    if (off_tri) std::memcpy(all, stream.data(), (size_t)off_tri * sizeof(float4));
+    for (size_t i = n_tri; i < 4u * pd_n; ++i) tri_pd[i] = 0.0f;
+    for (size_t m = 0; m < inst.size(); ++m) {
+        MeshInst& mi = inst[m];
+        const Src sm = src[m];
+        if (mi.tri_count == 0) continue;
+        const unsigned n_thr = mi.tri_count < 65536u ? 1u : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+        std::vector<double> sums(4u * n_thr, 0.0);            // per thread: centroid sums, then the largest squared distance
+        std::atomic<bool> bad_index{false};
+        auto for_faces = [&](auto&& body) {
+            const uint32_t per = (mi.tri_count + n_thr - 1u) / n_thr;
+            std::vector<std::thread> pool;
+            for (unsigned t = 1; t < n_thr; ++t)
+                pool.emplace_back([&, t] { body(std::min(mi.tri_count, t * per), std::min(mi.tri_count, (t + 1u) * per), t); });
+            body(0u, std::min(mi.tri_count, per), 0u);
+            for (auto& th : pool) th.join();
+        };
+        for_faces([&](uint32_t f0, uint32_t f1, unsigned t) {
             double cx = 0, cy = 0, cz = 0;
-            std::vector<const float*> corners;
-            for (uint32_t f = 0; f < me.face_count; ++f) {
+            for (uint32_t f = f0; f < f1; ++f) {
                 const float* P[3];
-                float2 uv[3];
+                const size_t tri = (size_t)mi.tri_first + f;
                 for (int j = 0; j < 3; ++j) {
-                    const uint64_t vi = (uint64_t)me.vertex_anchor + idx[me.index_anchor + 3 * f + j];  // kernels/raytracer.cl:93-99
-                    if (vi >= d->n_vertices) return fail(RT_ERR_INVALID, "mesh %u: vertex index out of bounds", M.mesh_anchor + k);
+                    const uint64_t vi = (uint64_t)sm.vertex_anchor + idx[sm.index_anchor + 3 * f + j];  // kernels/raytracer.cl:93-99
+                    if (vi >= d->n_vertices) { bad_index = true; return; }
                     P[j] = vtx + 4 * vi;
-                    uv[j] = (uvs && vi < d->n_uvs) ? make_float2(uvs[2 * vi], uvs[2 * vi + 1]) : make_float2(0.0f, 0.0f);
-                    corners.push_back(P[j]);
+                    tri_uv[3 * tri + j] = (uvs && vi < d->n_uvs) ? make_float2(uvs[2 * vi], uvs[2 * vi + 1]) : make_float2(0.0f, 0.0f);
                     cx += P[j][0]; cy += P[j][1]; cz += P[j][2];
                 }
                 float e1[3], e2[3];
@@ -238,32 +287,41 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
                 sub3(P[2], P[0], e2);
                 const float nx = e1[1] * e2[2] - e1[2] * e2[1], ny = e1[2] * e2[0] - e1[0] * e2[2], nz = e1[0] * e2[1] - e1[1] * e2[0];
                 const float inv = 1.0f / std::sqrt(nx * nx + ny * ny + nz * nz);
-                stream.push_back(make_float4(P[0][0], P[0][1], P[0][2], e1[0]));
-                stream.push_back(make_float4(e1[1], e1[2], e2[0], e2[1]));
-                stream.push_back(make_float4(e2[2], nx * inv, ny * inv, nz * inv));
+                float4* T = all + off_tri + 3 * tri;
+                T[0] = make_float4(P[0][0], P[0][1], P[0][2], e1[0]);
+                T[1] = make_float4(e1[1], e1[2], e2[0], e2[1]);
+                T[2] = make_float4(e2[2], nx * inv, ny * inv, nz * inv);
                 {   // plane offset for the conservative front-side filter (not parity relevant: it only removes
                     // triangles whose hit parameter would be negative); margin covers float rounding on the device
                     const double nd[3] = {(double)(nx * inv), (double)(ny * inv), (double)(nz * inv)};
                     const double pd = nd[0] * P[0][0] + nd[1] * P[0][1] + nd[2] * P[0][2];
-                    tri_pd.push_back((float)(pd - 4e-6 * (1.0 + std::fabs(pd))));
+                    tri_pd[tri] = (float)(pd - 4e-6 * (1.0 + std::fabs(pd)));
                 }
-                tri_uv.push_back(uv[0]); tri_uv.push_back(uv[1]); tri_uv.push_back(uv[2]);
-                tri_mesh.push_back((uint32_t)inst.size());
-                tri_face.push_back(mi.face_id_base + f);
-                ++n_tri;
+                tri_mesh[tri] = (uint32_t)m;
+                tri_face[tri] = mi.face_id_base + f;
             }
-            if (!corners.empty()) {
-                cx /= corners.size(); cy /= corners.size(); cz /= corners.size();
-                double r2 = 0;
-                for (const float* q : corners) {
+            sums[4 * t] = cx; sums[4 * t + 1] = cy; sums[4 * t + 2] = cz;
+        });
+        if (bad_index) return fail(RT_ERR_INVALID, "mesh %u: vertex index out of bounds", sm.mesh);
+        // conservative bounding sphere of the instance: centroid of the face corners + largest distance, inflated
+        double cx = 0, cy = 0, cz = 0;
+        for (unsigned t = 0; t < n_thr; ++t) { cx += sums[4 * t]; cy += sums[4 * t + 1]; cz += sums[4 * t + 2]; }
+        const double n_corners = 3.0 * mi.tri_count;
+        cx /= n_corners; cy /= n_corners; cz /= n_corners;
+        for_faces([&](uint32_t f0, uint32_t f1, unsigned t) {
+            double r2 = 0;
+            for (uint32_t f = f0; f < f1; ++f)
+                for (int j = 0; j < 3; ++j) {
+                    const float* q = vtx + 4 * ((uint64_t)sm.vertex_anchor + idx[sm.index_anchor + 3 * f + j]);
                     const double dx = q[0] - cx, dy = q[1] - cy, dz = q[2] - cz;
                     r2 = std::fmax(r2, dx * dx + dy * dy + dz * dz);
                 }
-                mi.bound[0] = (float)cx; mi.bound[1] = (float)cy; mi.bound[2] = (float)cz;
-                mi.bound[3] = (float)(std::sqrt(r2) * 1.001 + 1e-4);
-            }
-            inst.push_back(mi);
-        }
+            sums[4 * t + 3] = r2;
+        });
+        double r2 = 0;
+        for (unsigned t = 0; t < n_thr; ++t) r2 = std::fmax(r2, sums[4 * t + 3]);
+        mi.bound[0] = (float)cx; mi.bound[1] = (float)cy; mi.bound[2] = (float)cz;
+        mi.bound[3] = (float)(std::sqrt(r2) * 1.001 + 1e-4);
     }
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         float t;
@@ -271,27 +329,19 @@ int convert_scene(rt_ctx* c, const rt_scene_desc* d) {
         mat.push_back(make_float4(t, mats[i].extra, 0.0f, 0.0f));
         mat.push_back(make_float4(mats[i].color[0], mats[i].color[1], mats[i].color[2], 0.0f));
     }
-    while (tri_pd.size() % 4) tri_pd.push_back(0.0f);
-    c->staged_bytes = (stream.size() + 3 * inst.size() + tri_pd.size() / 4) * sizeof(float4) + (kTraceThreads / 32) * 1024u;
+    if (!inst.empty()) std::memcpy(all + stream_f4, inst.data(), inst.size() * sizeof(MeshInst));
+    c->staged_bytes = all_f4 * sizeof(float4) + (kTraceThreads / 32) * 1024u;
     c->n_finite = d->n_spheres + d->n_lenses + n_tri;
     if (c->prm.accel == RT_ACCEL_BRUTE && c->staged_bytes > kMaxStagedBytes)
         return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu); use RT_ACCEL_AUTO or RT_ACCEL_BVH",
                     c->staged_bytes, kMaxStagedBytes);
 
-    // one contiguous device buffer with the layout the kernels stage into shared memory:
-    // [test stream | mesh-instance table (3 x 16 B each) | plane offsets (padded to x4)]
-    const size_t stream_f4 = stream.size();
-    std::vector<float4> all(stream);
-    all.resize(stream_f4 + 3 * inst.size() + tri_pd.size() / 4);
-    if (!inst.empty()) std::memcpy(all.data() + stream_f4, inst.data(), inst.size() * sizeof(MeshInst));
-    if (!tri_pd.empty()) std::memcpy(all.data() + stream_f4 + 3 * inst.size(), tri_pd.data(), tri_pd.size() * sizeof(float));
-
     cudaStream_t s = c->stream;
-    CU(c->b_stream.upload(all, s));          CU(c->b_sph_shade.upload(sph_shade, s)); CU(c->b_sph_mat.upload(sph_mat, s));
+    CU(c->b_stream.upload(all, all_f4, s));  CU(c->b_sph_shade.upload(sph_shade, s)); CU(c->b_sph_mat.upload(sph_mat, s));
     CU(c->b_pla_normal.upload(pla_normal, s)); CU(c->b_pla_mat.upload(pla_mat, s));
     CU(c->b_len_shade.upload(len_shade, s)); CU(c->b_len_mat.upload(len_mat, s));
-    CU(c->b_tri_uv.upload(tri_uv, s));       CU(c->b_tri_mesh.upload(tri_mesh, s));
-    CU(c->b_tri_face.upload(tri_face, s));   CU(c->b_mat.upload(mat, s));
+    CU(c->b_tri_uv.upload(tri_uv, 3u * (size_t)n_tri, s)); CU(c->b_tri_mesh.upload(tri_mesh, n_tri, s));
+    CU(c->b_tri_face.upload(tri_face, n_tri, s)); CU(c->b_mat.upload(mat, s));
     CU(cudaStreamSynchronize(s));
 
     DevScene& sc = c->sc;
@@ -466,6 +516,7 @@ int rt_destroy(rt_ctx* c) {
         Guard g(c);
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
         rt_close_peers(c);
+        if (c->h_stage) cudaFreeHost(c->h_stage);
         cudaFree(c->d_certify);
         cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch); cudaFree(c->d_partial);
         cudaFree(c->d_block_cost); cudaFree(c->d_block_sorted); cudaFree(c->d_block_iota); cudaFree(c->d_block_order); cudaFree(c->d_block_scratch);
