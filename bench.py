@@ -286,7 +286,8 @@ def main_b200(a):
 
     # ---- end to end through the C ABI with HOST buffers: every step uploads scene, textures, table (pinned
     # host memory -> device), renders, reduces, finalizes and reads the image back to the host.
-    img_host = np.empty((H, W, 4), np.float32)
+    img_pinned = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()   # the caller's host image buffer (pinned, like the inputs)
+    img_host = img_pinned.numpy()
     tex_pinned = torch.from_numpy(tex).pin_memory()
     table_pinned = torch.from_numpy(table).pin_memory()
     h2d = tex_pinned.numel() * 4 + table_pinned.numel() * 4 + sum(v.nbytes for v in arr.values()) + 48
