@@ -174,6 +174,11 @@ int rt_scene_upload(const rt_scene* scene, rt_ctx* ctx);       /* SceneCreator::
 int rt_scene_free(rt_scene* scene);
 /* Camera(fov, aspect, pos, yaw, pitch).transferData() (src/camera.cpp:46-51, 94-118). */
 int rt_camera_data(int fov_degrees, float aspect, const float pos[3], float yaw, float pitch, float out[12]);
+/* The Camera controls main.cpp drives from GLFW callbacks (src/camera.cpp:53-92), applied in order to a camera built as
+ * above: ops = n_ops x (code, a, b) with code 0..3 move FORWARD / BACK / LEFT / RIGHT by dt = a, 4 rotate(a, b),
+ * 5 zoom(a), 6 setFasterSpeed(a != 0), 7 setSlowerSpeed(a != 0), 8 setSize(a); out = transferData() afterwards. */
+int rt_camera_run(int fov_degrees, float aspect, const float pos[3], float yaw, float pitch, const float* ops, int n_ops,
+                  float out[12]);
 /* Uncompressed 24-bit TGA of the (sqrt(mean),1) image, layout of main.cpp:262-289 (18-byte header, BGR, bottom-up),
  * values clamped to [0,1].  The reference reads the GL front buffer; here the float image is converted. */
 int rt_write_tga(const char* path, const float* rgba, int width, int height);

@@ -55,6 +55,29 @@ int rt_camera_data(int fov, float aspect, const float pos[3], float yaw, float p
     return RT_OK;
 }
 
+int rt_camera_run(int fov, float aspect, const float pos[3], float yaw, float pitch, const float* ops, int n_ops, float out[12]) {
+    if (!out || n_ops < 0 || (n_ops > 0 && !ops)) return rt_set_error_message(RT_ERR_INVALID, "rt_camera_run: bad argument");
+    Camera cam(fov, aspect, pos ? glm::vec3(pos[0], pos[1], pos[2]) : glm::vec3(0.0f), yaw, pitch);
+    for (int i = 0; i < n_ops; ++i) {
+        const int code = (int)ops[3 * i];
+        const float a = ops[3 * i + 1], b = ops[3 * i + 2];
+        switch (code) {
+            case 0: cam.move(FORWARD, a); break;
+            case 1: cam.move(BACK, a); break;
+            case 2: cam.move(LEFT, a); break;
+            case 3: cam.move(RIGHT, a); break;
+            case 4: cam.rotate(a, b); break;
+            case 5: cam.zoom(a); break;
+            case 6: cam.setFasterSpeed(a != 0.0f); break;
+            case 7: cam.setSlowerSpeed(a != 0.0f); break;
+            case 8: cam.setSize(a); break;
+            default: return rt_set_error_message(RT_ERR_INVALID, "rt_camera_run: unknown control code");
+        }
+    }
+    std::memcpy(out, cam.transferData(), 12 * sizeof(float));
+    return RT_OK;
+}
+
 int rt_write_tga(const char* path, const float* rgba, int w, int h) {
     if (!path || !rgba || w <= 0 || h <= 0 || w > 65535 || h > 65535) return rt_set_error_message(RT_ERR_INVALID, "rt_write_tga: bad argument");
     FILE* f = std::fopen(path, "wb");

@@ -82,6 +82,7 @@ def lib():
         "rt_scene_get_textures": [vp, C.POINTER(vp), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)],
         "rt_scene_upload": [vp, vp], "rt_scene_free": [vp],
         "rt_camera_data": [ci, C.c_float, vp, C.c_float, C.c_float, vp], "rt_write_tga": [C.c_char_p, vp, ci, ci],
+        "rt_camera_run": [ci, C.c_float, vp, C.c_float, C.c_float, vp, ci, vp],
     }
     for name, args in sig.items():
         f = getattr(L, name)
@@ -159,6 +160,18 @@ def camera_data(fov, aspect, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):
     out = np.zeros(12, np.float32)
     p = np.asarray(pos, np.float32)
     _check(lib().rt_camera_data(int(fov), float(aspect), p.ctypes.data, float(yaw), float(pitch), out.ctypes.data))
+    return out
+
+
+CAM_FORWARD, CAM_BACK, CAM_LEFT, CAM_RIGHT, CAM_ROTATE, CAM_ZOOM, CAM_FAST, CAM_SLOW, CAM_SIZE = range(9)
+
+
+def camera_run(fov, aspect, pos, yaw, pitch, ops):
+    """Camera(...) followed by the controls in ops = [(code, a, b), ...] (rt_camera_run); returns transferData()."""
+    out = np.zeros(12, np.float32)
+    p = np.asarray(pos, np.float32)
+    o = np.ascontiguousarray(np.asarray(ops, np.float32).reshape(-1, 3))
+    _check(lib().rt_camera_run(int(fov), float(aspect), p.ctypes.data, float(yaw), float(pitch), o.ctypes.data, len(o), out.ctypes.data))
     return out
 
 

@@ -19,6 +19,7 @@ from __future__ import annotations
 
 import ctypes
 import ctypes.util
+import math
 import os
 import re
 
@@ -506,6 +507,66 @@ def camera_data(fov_deg, aspect, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):
     horizontal = f32(2.0) * half_width * u
     vertical = f32(2.0) * half_height * v
     return np.concatenate([np.asarray(pos, dtype=f32), llc, horizontal, vertical]).astype(f32)
+
+
+class CameraPy:
+    """The reference's Camera with its controls (src/camera.cpp:16-118), float for float: move / rotate / zoom, the two
+    speed switches, setSize, and the two spellings of degrees -> radians (constructor: fov*M_PI/180.0f, setFov:
+    fov*M_PI*0.0055556f, both evaluated in double and stored to a float)."""
+    SLOW, NORMAL, FAST = f32(0.3), f32(1.0), f32(5.0)          # :16-18
+    SENS, ZOOM_MIN, ZOOM_MAX, ZOOM_SPEED = f32(0.2), f32(90.0), f32(10.0), f32(0.5)   # :19-22
+
+    def __init__(self, fov_deg, aspect, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):     # :46-51
+        self.fov, self.aspect = f32(int(fov_deg)), f32(aspect)
+        self.pos = np.asarray(pos, dtype=f32).copy()
+        self.yaw, self.pitch, self.speed = f32(yaw), f32(pitch), self.SLOW
+        angle = f32(np.float64(self.fov) * np.float64(np.pi) / np.float64(f32(180.0)))
+        self.half_height = _tanf(angle * f32(0.5))
+        self.half_width = self.aspect * self.half_height
+        self._update()
+
+    def _update(self):                                          # updateVectors, :26-37
+        rp, ry = glm_radians(self.pitch), glm_radians(self.yaw)
+        w = np.array([_cosf(rp) * _sinf(ry), _sinf(rp), _cosf(rp) * _cosf(ry)], dtype=f32)
+        self.w = _glm_normalize(w)
+        self.u = _glm_normalize(_cross(self.w, np.array([0.0, -1.0, 0.0], dtype=f32)))
+        self.v = _cross(self.u, self.w)
+
+    def _set_fov(self):                                         # :39-44
+        angle = f32(np.float64(self.fov) * np.float64(np.pi) * np.float64(f32(0.0055556)))
+        self.half_height = _tanf(angle * f32(0.5))
+        self.half_width = self.aspect * self.half_height
+        self._update()
+
+    def move(self, direction, dt):                              # :53-59; 0 forward, 1 back, 2 left, 3 right
+        ds = self.speed * f32(dt)
+        step = ((self.w if direction < 2 else self.u) * ds).astype(f32)
+        self.pos = (self.pos + step if direction in (0, 3) else self.pos - step).astype(f32)
+
+    def rotate(self, x, y):                                     # :61-70
+        self.yaw = f32(self.yaw + f32(x) * self.SENS * self.fov / self.ZOOM_MAX)
+        self.pitch = f32(self.pitch + f32(y) * self.SENS * self.fov / self.ZOOM_MAX)
+        self.pitch = min(max(self.pitch, f32(-89.0)), f32(89.0))
+        self.yaw = f32(math.fmod(float(self.yaw), 360.0))       # fmod of floats is exact
+        self._update()
+
+    def zoom(self, scroll):                                     # :72-77
+        self.fov = f32(self.fov + f32(scroll) * self.ZOOM_SPEED)
+        self.fov = min(max(self.fov, self.ZOOM_MAX), self.ZOOM_MIN)
+        self._set_fov()
+
+    def set_faster_speed(self, on): self.speed = self.FAST if on else self.NORMAL     # :79-82
+    def set_slower_speed(self, on): self.speed = self.SLOW if on else self.NORMAL     # :84-87
+
+    def set_size(self, aspect):                                 # :89-92
+        self.aspect = f32(aspect)
+        self._set_fov()
+
+    def data(self):                                             # transferData, :94-118 (+ the tail of updateVectors)
+        llc = self.w - (self.half_width * self.u + self.half_height * self.v)
+        horizontal = f32(2.0) * self.half_width * self.u
+        vertical = f32(2.0) * self.half_height * self.v
+        return np.concatenate([self.pos, llc, horizontal, vertical]).astype(f32)
 
 
 def _cross(a, b):

@@ -166,3 +166,37 @@ def test_random_scene_files_match_python_restatement(tmp_path, seed):
     want = sc.arrays()
     assert_same_scene(arr, want)
     assert np.array_equal(tex.view(np.uint32), sp.texture_from_rgba8(want["textures_rgba8"]).view(np.uint32))
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_camera_controls_match_python_restatement(seed):
+    """Camera::move / rotate / zoom / setFasterSpeed / setSlowerSpeed / setSize (src/camera.cpp:53-92) through
+    rt_camera_run against the numpy restatement, bit for bit, on seeded random control sequences — including the pitch
+    clamp at +-89, yaw wrapping at 360, the fov limits 10..90 and setFov's 0.0055556 spelling of pi/180."""
+    import rtb200
+    rng = np.random.default_rng(77 + seed)
+    fov, aspect = int(rng.integers(20, 90)), float(np.float32(rng.uniform(0.8, 2.4)))
+    pos = rng.uniform(-3, 3, 3).astype(np.float32)
+    yaw, pitch = float(np.float32(rng.uniform(-200, 400))), float(np.float32(rng.uniform(-80, 80)))
+    ops = []
+    for _ in range(int(rng.integers(5, 60))):
+        code = int(rng.integers(0, 9))
+        a = float(np.float32(rng.uniform(-40, 40) if code == 5 else rng.uniform(-300, 300) if code == 4 else rng.uniform(0.0, 2.5)))
+        b = float(np.float32(rng.uniform(-300, 300)))
+        if code in (6, 7):
+            a = float(rng.integers(0, 2))
+        ops.append((code, a, b))
+    cam = sp.CameraPy(fov, aspect, pos, yaw, pitch)
+    for code, a, b in ops:
+        if code < 4: cam.move(code, a)
+        elif code == 4: cam.rotate(a, b)
+        elif code == 5: cam.zoom(a)
+        elif code == 6: cam.set_faster_speed(a != 0)
+        elif code == 7: cam.set_slower_speed(a != 0)
+        else: cam.set_size(a)
+    got = rtb200.camera_run(fov, aspect, pos, yaw, pitch, ops)
+    assert np.array_equal(got.view(np.uint32), cam.data().view(np.uint32)), (got, cam.data())
+    assert np.array_equal(rtb200.camera_run(fov, aspect, pos, yaw, pitch, []).view(np.uint32),
+                          rtb200.camera_data(fov, aspect, pos, yaw, pitch).view(np.uint32))
+    with pytest.raises(rtb200.RtError):
+        rtb200.camera_run(fov, aspect, pos, yaw, pitch, [(9, 0, 0)])
