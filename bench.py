@@ -27,6 +27,8 @@ TABLE_SEED = 12345
 MESH_MODE = 0          # RT_MESH_FIRST_FRONT (the reference's rule); the LBVH configs use RT_MESH_NEAREST
 CONFIG = "c2"
 SLOTS_PER_RAY = 867.0   # measured FP32 issue slots per ray of the reference algorithm, default scene
+SLOTS_SOURCE = ("SURVEY.md 8(d): 1151 unfused FP32 operations per ray - 283 FMA-fusable pairs, default scene; tools/opcount.py "
+                "(the reference kernel run with an operation-counting float) re-measures 1152 operations per ray")
 METRIC = "Mrays/s at 1080p per scene, 1/2/4/8 B200, vs reference OpenCL on host CPU"
 WORKLOAD = "C2: default scene (8 spheres, 1 plane, 1 lens, 2 textured cubes = 24 triangles), 1920x1080, 1024 spp, max depth 30"
 
@@ -61,7 +63,7 @@ def parse():
 
 def select_config(a):
     """c2 is the bench line; the other BASELINE configs are reported with the same code for DESIGN.md."""
-    global W, H, SPP, DEPTH, WORKLOAD, MESH_MODE, CONFIG, SLOTS_PER_RAY
+    global W, H, SPP, DEPTH, WORKLOAD, MESH_MODE, CONFIG, SLOTS_PER_RAY, SLOTS_SOURCE
     CONFIG = a.config
     if a.config == "c1":
         W, H, SPP, DEPTH = 800, 600, 16, 8
@@ -69,7 +71,11 @@ def select_config(a):
     elif a.config == "c3":
         W, H, SPP, DEPTH = 1920, 1080, 4096, 30
         WORKLOAD = "C3: reference cube meshes (textured) + diffuse/dielectric/reflective spheres, 1920x1080, 4096 spp, max depth 30"
-        SLOTS_PER_RAY = None
+        # tools/opcount.py c3: 1005 operations per ray, 224 fusable pairs by its own (stricter) pairing rule; scaled to the
+        # SURVEY's pairing convention (283 pairs where the tool finds 237 on the default scene): 1005 - 224 * 283 / 237
+        SLOTS_PER_RAY = 738.0
+        SLOTS_SOURCE = ("tools/opcount.py c3 (the reference kernel run with an operation-counting float): 1005 FP32 operations per ray, "
+                        "224 FMA-fusable pairs scaled by 283/237 to SURVEY.md 8(d)'s pairing convention")
     elif a.config == "c4":
         W, H, SPP, DEPTH, MESH_MODE = 3840, 2160, 64, 30, 1
         WORKLOAD = "C4: synthetic closed mesh of 1 310 720 triangles + 1001 spheres + floor plane, 3840x2160, GPU-built LBVH, max depth 30"
@@ -358,10 +364,11 @@ def main_b200(a):
                          "kernel": kernel, "kernel_ms": round(k_ms, 3),
                          "achieved_executed": round(executed, 1),
                          "frac_executed": round(executed / peak_gslots, 4) if (peak_gslots and SLOTS_PER_RAY) else None,
-                         "note": "achieved = 867 slots x path segments of the launch (the reference algorithm's work for this image) / "
+                         "note": "achieved = slots_per_ray x path segments of the launch (the reference algorithm's work for this image) / "
                                  "kernel time; achieved_executed counts only the nearest-hit queries the kernel ran: the head of a "
                                  "path (same for every sample of a pixel) is traced once per pixel, not once per sample, so frac can exceed 1",
-                         "slots_per_ray": SLOTS_PER_RAY, "rays_per_launch": int(rays_launch),
+                         "slots_per_ray": SLOTS_PER_RAY, "slots_source": SLOTS_SOURCE if SLOTS_PER_RAY else None,
+                         "rays_per_launch": int(rays_launch),
                          "peak_source": "measured live: dependent-free FFMA loop on all SMs (rt_measure_fp32_peak); "
                                         "MEASURED_PEAKS.json has no FP32 entry",
                          "hbm": {"achieved_gbs": round(alg_bytes / (k_ms * 1e-3) / 1e9, 2), "peak_gbs": hbm_peak,

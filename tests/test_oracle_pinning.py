@@ -120,3 +120,23 @@ def test_sum_accumulation_equals_mean_of_samples(port, scenes, table):
     a0, _, _ = port.render(d, tex, cam, table, W, H, 0, 2, port.params(max_depth=30, accum_mode=op.ACCUM_SUM))
     a1, _, _ = port.render(d, tex, cam, table, W, H, 2, 3, port.params(max_depth=30, accum_mode=op.ACCUM_SUM))
     assert np.abs((a0 + a1) - acc).max() < 1e-5
+
+
+def test_op_counting_build_reproduces_the_survey_figures():
+    """tools/opcount.py (oracle/ref_opcount.cpp: the reference kernel with an operation-counting float) on the default
+    scene against SURVEY.md §8(d): 536 add/sub + 481 mul + 98 compare/min + 31 div + 3.9 sqrt = 1151 operations per ray,
+    2.34 rays per pixel-sample — the numerator of bench.py's roofline."""
+    import importlib.util
+    import os
+    lib = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libref_opcount.so")
+    if not os.path.exists(lib):
+        pytest.skip("oracle/_ref/libref_opcount.so not built")
+    spec = importlib.util.spec_from_file_location("opcount", os.path.join(os.path.dirname(lib), "..", "..", "tools", "opcount.py"))
+    oc = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(oc)
+    r = oc.count("default", 240, 135, 2, 30)
+    p = r["per_ray"]
+    assert abs(r["rays_per_pixel_sample"] - 2.344) < 0.03
+    assert abs(r["ops_per_ray"] - 1151) < 12
+    assert abs(p["add_sub"] - 536) < 6 and abs(p["mul"] - 481) < 6 and abs(p["compare"] - 98) < 3 and abs(p["sqrt"] - 3.9) < 0.1
+    assert 850 < r["slots_per_ray"] < 930          # 867 with the survey's pairing of mul -> add, 915 with this tool's
