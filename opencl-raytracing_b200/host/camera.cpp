@@ -1,81 +1,108 @@
-// host/camera.cpp — Camera of the reference (src/camera.cpp) restated; constants of src/camera.cpp:16-23.
+// host/camera.cpp — the camera behind include/camera.h.  Behaviour (and float rounding) of the reference's
+// src/camera.cpp; structure is this repository's: a Controls record, a derived Frame, and the 12-float block built on
+// demand.  Citations "ref:" point into the reference's src/camera.cpp.
 #include "../../include/camera.h"
 
 #include <cmath>
 
 namespace {
-const float kSpeedSlow = 0.3f, kSpeedNormal = 1.0f, kSpeedFast = 5.0f;   // src/camera.cpp:16-18
-const float kMouseSensitivity = 0.2f;                                    // :19
-const float kZoomMin = 90.0f, kZoomMax = 10.0f, kZoomSpeed = 0.5f;       // :20-22 (fov limits, sic)
-const glm::vec3 kUp(0.0f, -1.0f, 0.0f);                                  // :23, "up" on screen is world -y
+
+// ref:16-22.  The two zoom limits are fields of view in degrees: zooming IN narrows the angle down to 10, OUT up to 90.
+struct Tuning {
+    float crawl = 0.3f, walk = 1.0f, run = 5.0f;      // units per second
+    float degrees_per_pixel = 0.2f;                    // at the narrowest field of view, scaled by fov / narrowest
+    float narrowest = 10.0f, widest = 90.0f, degrees_per_scroll = 0.5f;
+    float pitch_limit = 89.0f;
+};
+const Tuning kTuning{};
+
+// The two spellings of degrees -> radians the reference uses for the field of view.  Both multiply in double (M_PI is
+// a double) and round once to float; they differ in the last bits, and each is kept where the reference has it.
+float fov_radians_by_division(float degrees) { return (float)(degrees * M_PI / 180.0f); }             // ref:47 (constructor)
+float fov_radians_by_reciprocal(float degrees) { return (float)(degrees * M_PI * 0.0055556f); }       // ref:40 (setFov)
+
 }  // namespace
 
-// src/camera.cpp:26-37
-void Camera::updateVectors() {
-    const float rp = glm::radians(pitch), ry = glm::radians(yaw);
-    w.x = glm::cos(rp) * glm::sin(ry);
-    w.y = glm::sin(rp);
-    w.z = glm::cos(rp) * glm::cos(ry);
-    w = glm::normalize(w);
-    u = glm::normalize(glm::cross(w, kUp));
-    v = glm::cross(u, w);
-    lower_left_corner = w - (half_width * u + half_height * v);
-    horizontal = 2.0f * half_width * u;
-    vertical = 2.0f * half_height * v;
+Camera::Camera(int camera_fov, float camera_aspect, const glm::vec3& pos, float y, float p) {
+    ctl.fov_degrees = (float)camera_fov;
+    ctl.aspect = camera_aspect;
+    ctl.units_per_second = kTuning.crawl;              // ref:46: a fresh camera moves at the slow speed
+    ctl.yaw_degrees = y;
+    ctl.pitch_degrees = p;
+    ctl.eye = pos;
+    open(fov_radians_by_division(ctl.fov_degrees));
 }
 
-// src/camera.cpp:39-44 — note the 0.0055556f (not pi/180 as in the constructor); both are kept
-void Camera::setFov() {
-    const float angle = (float)(fov * M_PI * 0.0055556f);
-    half_height = std::tan(angle * 0.5f);
-    half_width = aspect * half_height;
-    updateVectors();
+// ref:26-33: forward from yaw / pitch (yaw 0 looks down +z), right = forward x (0,-1,0), up = right x forward —
+// "up" on the screen is world -y.
+void Camera::orient() {
+    const float pitch = glm::radians(ctl.pitch_degrees), yaw = glm::radians(ctl.yaw_degrees);
+    glm::vec3 f;
+    f.x = glm::cos(pitch) * glm::sin(yaw);
+    f.y = glm::sin(pitch);
+    f.z = glm::cos(pitch) * glm::cos(yaw);
+    frame.forward = glm::normalize(f);
+    frame.right = glm::normalize(glm::cross(frame.forward, glm::vec3(0.0f, -1.0f, 0.0f)));
+    frame.up = glm::cross(frame.right, frame.forward);
 }
 
-// src/camera.cpp:46-51
-Camera::Camera(int camera_fov, float camera_aspect, const glm::vec3& pos, float y, float p)
-    : fov((float)camera_fov), aspect(camera_aspect), speed(kSpeedSlow), yaw(y), pitch(p), position(pos) {
-    const float angle = (float)(fov * M_PI / 180.0f);
-    half_height = std::tan(angle * 0.5f);
-    half_width = aspect * half_height;
-    updateVectors();
+// ref:41-43 / 48-50: image plane at distance 1
+void Camera::open(float vertical_angle_radians) {
+    frame.tan_half_vertical = std::tan(vertical_angle_radians * 0.5f);
+    frame.tan_half_horizontal = ctl.aspect * frame.tan_half_vertical;
+    orient();
 }
 
-// src/camera.cpp:53-59
+// ref:53-59
 void Camera::move(CameraMovementDirection dir, float dt) {
-    const float ds = speed * dt;
-    if (dir == FORWARD) position += w * ds;
-    else if (dir == BACK) position -= w * ds;
-    else if (dir == LEFT) position -= u * ds;
-    else if (dir == RIGHT) position += u * ds;
+    const float distance = ctl.units_per_second * dt;
+    switch (dir) {
+        case FORWARD: ctl.eye += frame.forward * distance; break;
+        case BACK:    ctl.eye -= frame.forward * distance; break;
+        case RIGHT:   ctl.eye += frame.right * distance; break;
+        case LEFT:    ctl.eye -= frame.right * distance; break;
+    }
 }
 
-// src/camera.cpp:61-70
+// ref:61-70: mouse deltas scaled with the field of view; pitch clamped short of the poles, yaw wrapped
 void Camera::rotate(float x, float y) {
-    yaw += x * kMouseSensitivity * fov / kZoomMax;
-    pitch += y * kMouseSensitivity * fov / kZoomMax;
-    if (pitch > 89.0f) pitch = 89.0f;
-    else if (pitch < -89.0f) pitch = -89.0f;
-    yaw = std::fmod(yaw, 360.0f);
-    updateVectors();
+    ctl.yaw_degrees += x * kTuning.degrees_per_pixel * ctl.fov_degrees / kTuning.narrowest;
+    ctl.pitch_degrees += y * kTuning.degrees_per_pixel * ctl.fov_degrees / kTuning.narrowest;
+    if (ctl.pitch_degrees > kTuning.pitch_limit) ctl.pitch_degrees = kTuning.pitch_limit;
+    else if (ctl.pitch_degrees < -kTuning.pitch_limit) ctl.pitch_degrees = -kTuning.pitch_limit;
+    ctl.yaw_degrees = std::fmod(ctl.yaw_degrees, 360.0f);
+    orient();
 }
 
-// src/camera.cpp:72-77
+// ref:72-77
 void Camera::zoom(float scroll) {
-    fov += scroll * kZoomSpeed;
-    if (fov < kZoomMax) fov = kZoomMax;
-    else if (fov > kZoomMin) fov = kZoomMin;
-    setFov();
+    float fov = ctl.fov_degrees + scroll * kTuning.degrees_per_scroll;
+    if (fov < kTuning.narrowest) fov = kTuning.narrowest;
+    else if (fov > kTuning.widest) fov = kTuning.widest;
+    ctl.fov_degrees = fov;
+    open(fov_radians_by_reciprocal(fov));
 }
 
-void Camera::setFasterSpeed(bool speed_up) { speed = speed_up ? kSpeedFast : kSpeedNormal; }      // :79-82
-void Camera::setSlowerSpeed(bool speed_down) { speed = speed_down ? kSpeedSlow : kSpeedNormal; }  // :84-87
-void Camera::setSize(float new_aspect) { aspect = new_aspect; setFov(); }                         // :89-92
+// ref:79-87: each switch falls back to the normal speed when released
+void Camera::setFasterSpeed(bool speed_up) { ctl.units_per_second = speed_up ? kTuning.run : kTuning.walk; }
+void Camera::setSlowerSpeed(bool speed_down) { ctl.units_per_second = speed_down ? kTuning.crawl : kTuning.walk; }
 
-// src/camera.cpp:94-118
+// ref:89-92
+void Camera::setSize(float new_aspect) {
+    ctl.aspect = new_aspect;
+    open(fov_radians_by_reciprocal(ctl.fov_degrees));
+}
+
+// ref:34-36 + 94-118: the block the render calls read.  Corner and extents depend on the frame only, so they are
+// formed here instead of being cached by every control.
 float* Camera::transferData() const {
-    static float data[12];
-    const glm::vec3* src[4] = {&position, &lower_left_corner, &horizontal, &vertical};
-    for (int i = 0; i < 4; ++i) { data[3 * i] = src[i]->x; data[3 * i + 1] = src[i]->y; data[3 * i + 2] = src[i]->z; }
-    return data;
+    static float block[12];
+    const glm::vec3 across = frame.tan_half_horizontal * frame.right, upward = frame.tan_half_vertical * frame.up;
+    const glm::vec3 corner = frame.forward - (across + upward);
+    const glm::vec3 horizontal = 2.0f * frame.tan_half_horizontal * frame.right;
+    const glm::vec3 vertical = 2.0f * frame.tan_half_vertical * frame.up;
+    const glm::vec3* rows[4] = {&ctl.eye, &corner, &horizontal, &vertical};
+    for (int r = 0; r < 4; ++r)
+        for (int k = 0; k < 3; ++k) block[3 * r + k] = (*rows[r])[k];
+    return block;
 }
