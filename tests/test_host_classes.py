@@ -200,3 +200,62 @@ def test_camera_controls_match_python_restatement(seed):
                           rtb200.camera_data(fov, aspect, pos, yaw, pitch).view(np.uint32))
     with pytest.raises(rtb200.RtError):
         rtb200.camera_run(fov, aspect, pos, yaw, pitch, [(9, 0, 0)])
+
+
+def _write_png_rgba(path, img, filter_type):
+    """Minimal PNG writer (8-bit RGBA, non-interlaced) that uses ONE filter type for every row — the files image tools
+    write mix them adaptively, so this is how each reconstruction rule of the reader (PNG spec 9.2) gets its own test."""
+    import struct
+    import zlib
+    h, w, _ = img.shape
+    raw = bytearray()
+    prev = np.zeros((w * 4,), np.int32)
+    for y in range(h):
+        cur = img[y].reshape(-1).astype(np.int32)
+        left = np.concatenate([np.zeros(4, np.int32), cur[:-4]])
+        upleft = np.concatenate([np.zeros(4, np.int32), prev[:-4]])
+        if filter_type == 0: pred = np.zeros_like(cur)
+        elif filter_type == 1: pred = left
+        elif filter_type == 2: pred = prev
+        elif filter_type == 3: pred = (left + prev) >> 1
+        else:
+            p = left + prev - upleft
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - upleft)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, upleft))
+        raw.append(filter_type)
+        raw += bytes(((cur - pred) & 255).astype(np.uint8))
+        prev = cur
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+    comp = zlib.compress(bytes(raw), 6)
+    half = len(comp) // 2                       # two IDAT chunks: the reader must concatenate them
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6, 0, 0, 0)) +
+                chunk(b"tEXt", b"Comment\x00filter %d" % filter_type) + chunk(b"IDAT", comp[:half]) + chunk(b"IDAT", comp[half:]) +
+                chunk(b"IEND", b""))
+
+
+@pytest.mark.parametrize("filter_type", range(5))
+def test_png_reader_every_filter_type(tmp_path, filter_type):
+    """The built-in PNG reader behind SceneCreator::loadTextures (the reference calls stbi_loadf, src/scene.cpp:158): every
+    row filter of the PNG spec, split IDAT, an ancillary chunk; texels = stb's float conversion of the decoded bytes."""
+    import shutil
+    import rtb200
+    rng = np.random.default_rng(5 + filter_type)
+    for f in ("shapes.obj", "shapes.mtl", "shapes.scene"):
+        shutil.copy(os.path.join(ASSETS, f), tmp_path / f)
+    imgs = []
+    for name in ("tex_a.png", "tex_b.png"):
+        img = rng.integers(0, 256, (32, 32, 4), dtype=np.uint8)
+        img[::3] = img[::3] // 64 * 64                      # some smooth rows, so that predictions matter
+        _write_png_rgba(str(tmp_path / name), img, filter_type)
+        imgs.append(img)
+    arr, tex = rtb200.load_scene_file("shapes.scene", str(tmp_path), str(tmp_path))
+    paths = [os.path.basename(p) for p in _texture_order(tmp_path)]
+    want = sp.texture_from_rgba8(np.stack([imgs[("tex_a.png", "tex_b.png").index(p)] for p in paths]))
+    assert tex.shape == want.shape and np.array_equal(tex.view(np.uint32), want.view(np.uint32))
+
+
+def _texture_order(tmp_path):
+    sc = sp.parse_scene_file(str(tmp_path / "shapes.scene"), root=str(tmp_path))
+    return sc.texture_paths
