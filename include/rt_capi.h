@@ -102,6 +102,10 @@ int rt_make_random_table(uint32_t seed, float* out_400000);
 int rt_set_random_table(rt_ctx* ctx, const float* table, uint32_t n_floats);
 int rt_set_params(rt_ctx* ctx, const rt_params* params);
 int rt_get_params(rt_ctx* ctx, rt_params* params);
+/* Restrict the render calls to the work-items [x0, x0+w) x [y0, y0+h) of the frame (a sub-NDRange with a global offset in
+ * the terms of src/raytracer.cpp:137, which always enqueues the whole frame): pixels outside keep their contents, the
+ * per-pixel RNG keys and primary rays are those of the full frame.  w <= 0 or h <= 0 restores the whole frame. */
+int rt_set_region(rt_ctx* ctx, int x0, int y0, int w, int h);
 
 /* RayTracer::render (src/raytracer.cpp:127-144): sample_counter = 0, one sample, overwrites the image. */
 int rt_render(rt_ctx* ctx, const float camera[12]);
@@ -182,6 +186,14 @@ int rt_camera_run(int fov_degrees, float aspect, const float pos[3], float yaw, 
 /* Uncompressed 24-bit TGA of the (sqrt(mean),1) image, layout of main.cpp:262-289 (18-byte header, BGR, bottom-up),
  * values clamped to [0,1].  The reference reads the GL front buffer; here the float image is converted. */
 int rt_write_tga(const char* path, const float* rgba, int width, int height);
+
+/* Counted work of LBVH renders (the roofline numerator of a BVH run is the work the run itself did, not the
+ * brute-force operation count of kernels/raytracer.cl:322-360).  While counting is on, fast-arithmetic renders of LBVH
+ * scenes go through an instrumented copy of the render kernel — same image, not to be timed — and rt_get_work_counts
+ * returns, for the last render call: [0] node visits (two box tests each), leaf tests of [1] spheres, [2] lenses,
+ * [3] triangles, [4] plane tests, [5] nearest-hit queries of the render kernel, [6..7] zero. */
+int rt_set_work_counting(rt_ctx* ctx, int on);
+int rt_get_work_counts(rt_ctx* ctx, uint64_t out[8]);
 
 /* Measured FP32 issue peak of the device (dependent-free FFMA loop on every SM): G lane-instructions/s. */
 int rt_measure_fp32_peak(int device, double* gslots_per_s, double* sm_clock_mhz);

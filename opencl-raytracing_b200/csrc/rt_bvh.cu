@@ -149,8 +149,24 @@ __device__ __forceinline__ Box child_box(int c, const Box* node_box, const Box* 
     return c < 0 ? prim_box[sorted[~c]] : node_box[c];
 }
 
+// curved[node] = 1 when the subtree holds a sphere or a lens: their binary32 tests report hits OUTSIDE the primitive from
+// far away (rt_kernels.cuh, slab<true>), so only those subtrees need the distance-proportional box inflation.
+// COHERENT: inside k_refit the value was written by another thread of this launch; it is read through L2 (ld.cg),
+// because an L1 line fetched earlier for a neighbouring entry may predate the write.
+template <bool COHERENT>
+__device__ __forceinline__ uint8_t child_curved(int c, const uint8_t* curved, const uint2* leaf_info, const uint32_t* sorted) {
+    if (c < 0) return (uint8_t)((leaf_info[sorted[~c]].x >> 28) != 4u);
+    return COHERENT ? __ldcg(curved + c) : curved[c];
+}
+__device__ __forceinline__ Box node_box_coherent(const Box* node_box, int c) {
+    Box b;
+    const float* f = reinterpret_cast<const float*>(node_box + c);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { b.lo[k] = __ldcg(f + k); b.hi[k] = __ldcg(f + 3 + k); }
+    return b;
+}
 __global__ void k_refit(int n, const int2* children, const int* parent, const uint32_t* sorted, const Box* prim_box,
-                        Box* node_box, unsigned int* visits) {
+                        Box* node_box, unsigned int* visits, const uint2* leaf_info, uint8_t* curved) {
     const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
     if (leaf >= n) return;
     int node = parent[n - 1 + leaf];
@@ -158,16 +174,18 @@ __global__ void k_refit(int n, const int2* children, const int* parent, const ui
         __threadfence();
         if (atomicAdd(&visits[node], 1u) == 0u) return;            // first arrival: the sibling subtree is not done yet
         const int2 ch = children[node];
-        const Box a = child_box(ch.x, node_box, prim_box, sorted), b = child_box(ch.y, node_box, prim_box, sorted);
+        const Box a = ch.x < 0 ? prim_box[sorted[~ch.x]] : node_box_coherent(node_box, ch.x);
+        const Box b = ch.y < 0 ? prim_box[sorted[~ch.y]] : node_box_coherent(node_box, ch.y);
         Box m;
         for (int k = 0; k < 3; ++k) { m.lo[k] = fminf(a.lo[k], b.lo[k]); m.hi[k] = fmaxf(a.hi[k], b.hi[k]); }
         node_box[node] = m;
+        curved[node] = child_curved<true>(ch.x, curved, leaf_info, sorted) | child_curved<true>(ch.y, curved, leaf_info, sorted);
         node = parent[node];
     }
 }
 
 __global__ void k_emit_nodes(BvhBuildInput in, int n, const int2* children, const uint32_t* sorted, const Box* prim_box, const Box* node_box,
-                             const uint2* leaf_info, BvhNode* nodes, float4* leaves) {
+                             const uint2* leaf_info, const uint8_t* curved, BvhNode* nodes, float4* leaves) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {                                        // leaf record: the primitive's words of the stream + its ids
         const uint2 info = leaf_info[sorted[i]];
@@ -183,7 +201,9 @@ __global__ void k_emit_nodes(BvhBuildInput in, int n, const int2* children, cons
     const Box a = child_box(ch.x, node_box, prim_box, sorted), b = child_box(ch.y, node_box, prim_box, sorted);
     BvhNode nd;
     for (int k = 0; k < 3; ++k) { nd.lo0[k] = a.lo[k]; nd.hi0[k] = a.hi[k]; nd.lo1[k] = b.lo[k]; nd.hi1[k] = b.hi[k]; }
-    nd.child0 = ch.x; nd.child1 = ch.y; nd.pad0 = nd.pad1 = 0u;
+    nd.child0 = ch.x; nd.child1 = ch.y;
+    nd.flags = (uint32_t)child_curved<false>(ch.x, curved, leaf_info, sorted) | ((uint32_t)child_curved<false>(ch.y, curved, leaf_info, sorted) << 1);
+    nd.pad1 = 0u;
     nodes[i] = nd;
 }
 
@@ -220,11 +240,12 @@ cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t st
     int2* children = nullptr;
     int* parent = nullptr;
     unsigned int* visits = nullptr;
+    uint8_t* curved = nullptr;
     BV(tmp.get(&prim_box, n)); BV(tmp.get(&centroids, n)); BV(tmp.get(&leaf_info, n)); BV(tmp.get(&cb, n)); BV(tmp.get(&scene, 1));
     BV(tmp.get(&keys, n)); BV(tmp.get(&keys_sorted, n)); BV(tmp.get(&vals, n)); BV(tmp.get(&sorted, n));
     BV(cudaMalloc(&out.leaves, (size_t)n * 4 * sizeof(float4)));
     BV(cudaMalloc(&out.nodes, (size_t)(n > 1 ? n - 1 : 1) * sizeof(BvhNode)));
-    out.n_leaves = n;
+    // out.n_leaves stays 0 until the last kernel has finished: a failed build must not look like a finished one
 
     k_prim_bounds<<<G, T, 0, st>>>(in, n, prim_box, centroids, leaf_info);
     k_centroid_bounds_in<<<G, T, 0, st>>>(centroids, n, cb);
@@ -242,17 +263,21 @@ cudaError_t build_lbvh(const BvhBuildInput& in, BvhBuffers& out, cudaStream_t st
     BV(tmp.get((char**)&sscratch, sbytes));
     BV(cub::DeviceRadixSort::SortPairs(sscratch, sbytes, keys, keys_sorted, vals, sorted, (int)n, 0, 64, st));
     if (n == 1) {
-        k_emit_nodes<<<1, 32, 0, st>>>(in, 1, nullptr, sorted, prim_box, nullptr, leaf_info, out.nodes, out.leaves);
+        k_emit_nodes<<<1, 32, 0, st>>>(in, 1, nullptr, sorted, prim_box, nullptr, leaf_info, nullptr, out.nodes, out.leaves);
         BV(cudaGetLastError());
-        return cudaStreamSynchronize(st);
+        BV(cudaStreamSynchronize(st));
+        out.n_leaves = n;
+        return cudaSuccess;
     }
-    BV(tmp.get(&children, n - 1)); BV(tmp.get(&parent, 2 * (size_t)n - 1)); BV(tmp.get(&visits, n - 1)); BV(tmp.get(&node_box, n - 1));
+    BV(tmp.get(&children, n - 1)); BV(tmp.get(&parent, 2 * (size_t)n - 1)); BV(tmp.get(&visits, n - 1)); BV(tmp.get(&node_box, n - 1)); BV(tmp.get(&curved, n - 1));
     BV(cudaMemsetAsync(visits, 0, (size_t)(n - 1) * sizeof(unsigned int), st));
     k_hierarchy<<<G, T, 0, st>>>(keys_sorted, (int)n, children, parent);
-    k_refit<<<G, T, 0, st>>>((int)n, children, parent, sorted, prim_box, node_box, visits);
-    k_emit_nodes<<<G, T, 0, st>>>(in, (int)n, children, sorted, prim_box, node_box, leaf_info, out.nodes, out.leaves);
+    k_refit<<<G, T, 0, st>>>((int)n, children, parent, sorted, prim_box, node_box, visits, leaf_info, curved);
+    k_emit_nodes<<<G, T, 0, st>>>(in, (int)n, children, sorted, prim_box, node_box, leaf_info, curved, out.nodes, out.leaves);
     BV(cudaGetLastError());
-    return cudaStreamSynchronize(st);
+    BV(cudaStreamSynchronize(st));
+    out.n_leaves = n;
+    return cudaSuccess;
 }
 
 }  // namespace rtb

@@ -12,7 +12,7 @@ namespace rtb {
 struct alignas(16) BvhNode {
     float lo0[3]; int32_t child0;
     float hi0[3]; int32_t child1;
-    float lo1[3]; uint32_t pad0;
+    float lo1[3]; uint32_t flags;     // bit 0 / 1: the subtree of child 0 / 1 holds a sphere or a lens (needs the inflated box test)
     float hi1[3]; uint32_t pad1;
 };
 static_assert(sizeof(BvhNode) == 64, "one node = four 16-byte words");

@@ -87,6 +87,7 @@ struct rt_ctx {
     float4* d_accum_own = nullptr;
     float4* d_accum = nullptr;      // own or caller-supplied
     unsigned long long* d_rays = nullptr;
+    unsigned long long* d_head_counts = nullptr;   // inside d_rays
     float* d_table = nullptr;
     float4* d_tex = nullptr;
     DevTexture tex{nullptr, 1, 1, 1};
@@ -103,6 +104,8 @@ struct rt_ctx {
     uint32_t n_finite = 0;            // spheres + lenses + triangles
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO, RT_HEAD_ON};
     uint32_t sample_counter = 0;
+    int rx0 = 0, ry0 = 0, rx1 = 0, ry1 = 0;   // render region (rt_set_region); the whole frame by default
+    int head_region[4] = {0, 0, 0, 0};
     int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
     // fast arithmetic: Exact primary-hit ids of the current (scene, camera, mesh rule), see ensure_certified()
     uint32_t* d_certify = nullptr;
@@ -113,7 +116,7 @@ struct rt_ctx {
     float4* d_head_rec = nullptr;
     uint8_t* d_head_flag = nullptr;
     uint32_t* d_head_list = nullptr;
-    uint32_t* d_head_count = nullptr;
+    uint32_t *d_head_key = nullptr, *d_head_key_sorted = nullptr, *d_head_iota = nullptr;
     void* d_head_scratch = nullptr;
     size_t head_scratch_bytes = 0;
     uint32_t head_n_slots = 0, head_n_stoch = 0;
@@ -136,6 +139,9 @@ struct rt_ctx {
     void* peer_image0 = nullptr;
     bool peer_opened[kMaxPeers] = {false};   // accum pointers obtained from cudaIpcOpenMemHandle
     bool peer_image_opened = false;
+    bool count_work = false;          // rt_set_work_counting: LBVH renders go through the instrumented (untimed) kernel
+    unsigned long long* d_work = nullptr;
+    uint64_t work_counts[8] = {0};
     rt_stats stats{};
 };
 
@@ -383,7 +389,14 @@ int ensure_accel(rt_ctx* c) {
     BvhBuildInput in{};
     in.stream = c->sc.stream; in.off_len = c->sc.off_len; in.off_tri = c->sc.off_tri;
     in.n_sph = c->sc.n_sph; in.n_len = c->sc.n_len; in.n_tri = c->sc.n_tri; in.tri_face_id = c->b_tri_face.p;
-    CU(build_lbvh(in, c->bvh, c->stream));
+    {   // a failed build leaves no half-built tree behind: the next render call retries (or fails again), never traverses garbage
+        const cudaError_t be = getenv("RTB200_TEST_FAIL_BVH_BUILD") ? cudaErrorMemoryAllocation : build_lbvh(in, c->bvh, c->stream);
+        if (be != cudaSuccess) {
+            free_lbvh(c->bvh);
+            c->stats.bvh_nodes = 0; c->certify_valid = false; c->head_valid = false;
+            return fail(RT_ERR_CUDA, "build_lbvh: %s", cudaGetErrorString(be));
+        }
+    }
     c->stats.bvh_nodes = c->bvh.n_leaves > 1 ? c->bvh.n_leaves - 1 : 1;
     c->stats.kernel_launches += 8;
     c->certify_valid = false;
@@ -423,17 +436,21 @@ int ensure_certified(rt_ctx* c, const float* cam) {
 int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
     *rebuilt = false;
     const bool bvh = c->bvh.n_leaves != 0;
+    const int region[4] = {c->rx0, c->ry0, c->rx1, c->ry1};
     if (c->head_valid && c->head_mesh_mode == c->prm.mesh_mode && c->head_depth == c->prm.max_depth && c->head_bvh == bvh &&
-        std::memcmp(c->head_cam, cam, 48) == 0)
+        std::memcmp(c->head_cam, cam, 48) == 0 && std::memcmp(c->head_region, region, sizeof region) == 0)
         return RT_OK;
     const uint32_t n_slots = (uint32_t)(((c->W + 7) / 8) * ((c->H + 3) / 4)) * 32u;
     if (!c->d_head_rec) {
         CU(cudaMalloc(&c->d_head_rec, (size_t)n_slots * 4 * sizeof(float4)));
         CU(cudaMalloc(&c->d_head_flag, n_slots));
         CU(cudaMalloc(&c->d_head_list, (size_t)n_slots * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->d_head_count, sizeof(uint32_t)));
+        CU(cudaMalloc(&c->d_head_key, (size_t)n_slots * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->d_head_key_sorted, (size_t)n_slots * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->d_head_iota, (size_t)n_slots * sizeof(uint32_t)));
+        CU(fill_iota(c->d_head_iota, n_slots, c->stream));
         size_t bytes = 0;
-        CU(partition_heads(c->d_head_flag, n_slots, c->d_head_list, c->d_head_count, nullptr, bytes, c->stream));
+        CU(sort_heads(c->d_head_key, c->d_head_key_sorted, c->d_head_iota, c->d_head_list, n_slots, nullptr, bytes, c->stream));
         CU(cudaMalloc(&c->d_head_scratch, bytes ? bytes : 1));
         c->head_scratch_bytes = bytes;
     }
@@ -441,22 +458,24 @@ int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
     L.sc = c->sc;
     std::memcpy(L.cam, cam, 48);
     L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth; L.mesh_mode = c->prm.mesh_mode; L.bvh = dev_bvh(c);
-    L.rec = c->d_head_rec; L.flag = c->d_head_flag; L.n_slots = n_slots; L.segments = c->d_rays + 2;
-    CU(cudaMemsetAsync(c->d_rays + 2, 0, sizeof(unsigned long long), c->stream));
+    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1;
+    L.key_mask = 0x3FFFu;
+    if (const char* e = std::getenv("RTB200_HEAD_SORT")) L.key_mask = (uint32_t)std::strtoul(e, nullptr, 0);   // A/B: 0 = slot order
+    L.rec = c->d_head_rec; L.flag = c->d_head_flag; L.key = c->d_head_key; L.n_slots = n_slots; L.segments = c->d_head_counts;
+    CU(cudaMemsetAsync(c->d_head_counts, 0, 2 * sizeof(unsigned long long), c->stream));
     CU(launch_head(L, c->stream));
     size_t bytes = c->head_scratch_bytes;
-    CU(partition_heads(c->d_head_flag, n_slots, c->d_head_list, c->d_head_count, c->d_head_scratch, bytes, c->stream));
-    uint32_t n_stoch = 0;
-    unsigned long long seg = 0;
-    CU(cudaMemcpyAsync(&n_stoch, c->d_head_count, sizeof n_stoch, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaMemcpyAsync(&seg, c->d_rays + 2, sizeof seg, cudaMemcpyDeviceToHost, c->stream));
+    CU(sort_heads(c->d_head_key, c->d_head_key_sorted, c->d_head_iota, c->d_head_list, n_slots, c->d_head_scratch, bytes, c->stream));
+    unsigned long long counts[2] = {0, 0};           // segments of the heads, stochastic slots
+    CU(cudaMemcpyAsync(counts, c->d_head_counts, sizeof counts, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->head_n_slots = n_slots; c->head_n_stoch = n_stoch; c->head_segments = seg;
+    c->head_n_slots = n_slots; c->head_n_stoch = (uint32_t)counts[1]; c->head_segments = counts[0];
     std::memcpy(c->head_cam, cam, 48);
+    std::memcpy(c->head_region, region, sizeof region);
     c->head_mesh_mode = c->prm.mesh_mode; c->head_depth = c->prm.max_depth; c->head_bvh = bvh;
     c->head_valid = true;
     c->order_valid = false;
-    c->stats.kernel_launches += 3;   // k_head + CUB's partition (init + sweep)
+    c->stats.kernel_launches += 4;   // k_head + CUB's radix sort of the 16-bit head keys (histogram, scan, 2 passes; onesweep)
     *rebuilt = true;
     return RT_OK;
 }
@@ -475,6 +494,9 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     *out = nullptr;
     if (width <= 0 || height <= 0 || width > 65535 || height > 65535)
         return fail(RT_ERR_INVALID, "rt_create: bad size %d x %d", width, height);
+    // pixel, slot and list counts are carried as 32-bit integers through the launch structs
+    if ((uint64_t)((width + 7) / 8) * (uint64_t)((height + 3) / 4) * 32u >= (1ull << 31))
+        return fail(RT_ERR_UNSUPPORTED, "rt_create: %d x %d exceeds the supported 2^31 pixel slots", width, height);
     int n_dev = 0;
     cudaError_t e = cudaGetDeviceCount(&n_dev);
     if (e != cudaSuccess || n_dev == 0)
@@ -483,6 +505,7 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     if (device < 0 || device >= n_dev) return fail(RT_ERR_INVALID, "rt_create: device %d out of range (0..%d)", device, n_dev - 1);
     rt_ctx* c = new rt_ctx();
     c->device = device; c->W = width; c->H = height;
+    c->rx1 = width; c->ry1 = height;
     Guard g(c);
     const size_t px = (size_t)width * height;
     auto bail = [&](cudaError_t err, const char* what) {
@@ -497,7 +520,8 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     if ((e = cudaEventCreate(&c->ev2)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaMalloc(&c->d_image, px * sizeof(float4))) != cudaSuccess) return bail(e, "image buffer");
     if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4))) != cudaSuccess) return bail(e, "accumulation buffer");
-    if ((e = cudaMalloc(&c->d_rays, 4 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counters");   // rays, queries, head segments
+    if ((e = cudaMalloc(&c->d_rays, 6 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counters");   // rays, queries, -, queue, head segments, stochastic slots
+    c->d_head_counts = c->d_rays + 4;
     c->d_accum = c->d_accum_own;
     cudaMemsetAsync(c->d_image, 0, px * sizeof(float4), c->stream);
     cudaMemsetAsync(c->d_accum, 0, px * sizeof(float4), c->stream);
@@ -517,8 +541,8 @@ int rt_destroy(rt_ctx* c) {
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
         rt_close_peers(c);
         if (c->h_stage) cudaFreeHost(c->h_stage);
-        cudaFree(c->d_certify);
-        cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_count); cudaFree(c->d_head_scratch); cudaFree(c->d_partial);
+        cudaFree(c->d_certify); cudaFree(c->d_work);
+        cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_key); cudaFree(c->d_head_key_sorted); cudaFree(c->d_head_iota); cudaFree(c->d_head_scratch); cudaFree(c->d_partial);
         cudaFree(c->d_block_cost); cudaFree(c->d_block_sorted); cudaFree(c->d_block_iota); cudaFree(c->d_block_order); cudaFree(c->d_block_scratch);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
         c->b_stream.release(); c->b_sph_shade.release(); c->b_pla_normal.release(); c->b_len_shade.release();
@@ -600,6 +624,24 @@ int rt_set_params(rt_ctx* c, const rt_params* p) {
     if (p->max_depth == 0) return fail(RT_ERR_INVALID, "max_depth must be >= 1");
     if (p->rng_mode > 2 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2 || p->path_head > 1) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
     c->prm = *p;
+    return RT_OK;
+}
+int rt_set_region(rt_ctx* c, int x0, int y0, int w, int h) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (w <= 0 || h <= 0) { c->rx0 = c->ry0 = 0; c->rx1 = c->W; c->ry1 = c->H; return RT_OK; }
+    if (x0 < 0 || y0 < 0 || x0 > c->W - w || y0 > c->H - h)
+        return fail(RT_ERR_INVALID, "rt_set_region: %d x %d at (%d, %d) does not lie inside the %d x %d frame", w, h, x0, y0, c->W, c->H);
+    c->rx0 = x0; c->ry0 = y0; c->rx1 = x0 + w; c->ry1 = y0 + h;
+    return RT_OK;
+}
+int rt_set_work_counting(rt_ctx* c, int on) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    c->count_work = on != 0;
+    return RT_OK;
+}
+int rt_get_work_counts(rt_ctx* c, uint64_t out[8]) {
+    if (!c || !out) return fail(RT_ERR_INVALID, "rt_get_work_counts: null argument");
+    for (int q = 0; q < 8; ++q) out[q] = c->work_counts[q];
     return RT_OK;
 }
 int rt_get_params(rt_ctx* c, rt_params* p) {
@@ -698,6 +740,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     std::memcpy(L.cam, cam, 12 * sizeof(float));
     L.W = c->W; L.H = c->H; L.first = first; L.n = n; L.depth = c->prm.max_depth;
+    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1;
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
@@ -722,7 +765,19 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
         CU(cudaEventRecord(c->ev2, c->stream));
         { int r = order_blocks(c, L, &extra_launches); if (r != RT_OK) return r; }     // may render the first samples
         { int r = plan_chunks(c, L); if (r != RT_OK) return r; }
-        CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_tail_strict(L, c->stream) : launch_trace_tail_fast(L, c->stream));
+        const bool counting = c->count_work && L.bvh.n_leaves && c->prm.arith == RT_ARITH_FAST;
+        if (counting) {
+            if (!c->d_work) CU(cudaMalloc(&c->d_work, 8 * sizeof(unsigned long long)));
+            CU(cudaMemsetAsync(c->d_work, 0, 8 * sizeof(unsigned long long), c->stream));
+            L.work = c->d_work;
+            CU(launch_trace_tail_fast_count(L, c->stream));
+            unsigned long long w[8];
+            CU(cudaMemcpyAsync(w, c->d_work, sizeof w, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            for (int q = 0; q < 8; ++q) c->work_counts[q] = w[q];
+        } else {
+            CU(c->prm.arith == RT_ARITH_STRICT ? launch_trace_tail_strict(L, c->stream) : launch_trace_tail_fast(L, c->stream));
+        }
         CU(launch_combine_chunks(L, c->stream));
     } else {
         CU(cudaEventRecord(c->ev2, c->stream));
@@ -743,6 +798,10 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     c->stats.rays_last = rays;
     c->stats.queries_last = use_head ? counters[1] + (head_rebuilt ? c->head_segments : 0ull) : counters[0];
     c->stats.rays_total += rays;
+    if (c->count_work && L.bvh.n_leaves) {       // tail-kernel queries of this call and their plane tests (every query scans the plane list)
+        c->work_counts[5] = counters[1];
+        c->work_counts[4] = counters[1] * (unsigned long long)c->sc.n_pla;
+    }
     c->stats.kernel_launches += (L.chunks > 1u ? 2 : 1) + extra_launches;
     return RT_OK;
 }

@@ -64,7 +64,9 @@ struct DevTexture {
 //   rec[2 * n_slots + s] = (out.rgb, hit bv)  rec[3 * n_slots + s] = (bounce index, hit id, hit aux, material id) as bits
 //   flag[s]: 0 outside the frame, 1 terminal (rec[2].rgb is the colour of every sample, rec[3].x the segment count),
 //            2 stochastic (restart state of the first random-consuming hit).
-// list[0, n_stoch) = stochastic slots in slot order; list[n_slots - n_rest, n_slots) = all other slots (reversed).
+// list[0, n_stoch) = stochastic slots ordered by (material type, primitive kind[, primitive]) of the head hit, slot order
+// inside a class, so that the lanes of a warp of k_trace_tail_* shade the same kind of surface on the first bounce of
+// every sample (84 % of the trips on C2); list[n_stoch, n_slots) = all other slots.
 struct DevHead {
     const float4* rec;
     const uint8_t* flag;
@@ -79,6 +81,7 @@ struct TraceLaunch {
     const float* table;        // 400 000 floats (table RNG) or nullptr
     float cam[12];             // src/camera.cpp:94-118
     int W, H;
+    int rx0, ry0, rx1, ry1;    // render region [rx0, rx1) x [ry0, ry1) of the frame (rt_set_region); pixels outside are untouched
     uint32_t first, n;         // samples [first, first + n)
     uint32_t depth;
     uint32_t rng_mode, seed, accum_mode, mesh_mode;
@@ -102,6 +105,9 @@ struct TraceLaunch {
     // block_order[i / chunks] instead of the blocks in list order.
     uint32_t* block_cost;
     const uint32_t* block_order;
+    // Instrumented LBVH kernel (k_trace_tail_fast_bvh_count, untimed): [0] node visits (two box tests each), leaf tests of
+    // [1] spheres, [2] lenses, [3] triangles.  nullptr in the timed kernels.
+    unsigned long long* work;
 };
 
 // k_head_*: the sample-independent head of every pixel's path (see rt_kernels.cuh, "path heads").
@@ -109,12 +115,15 @@ struct HeadLaunch {
     DevScene sc;
     float cam[12];
     int W, H;
+    int rx0, ry0, rx1, ry1;    // render region: slots outside it are flagged kHeadDead
     uint32_t depth, mesh_mode;
     DevBvh bvh;
     float4* rec;               // 4 x n_slots
     uint8_t* flag;             // n_slots
+    uint32_t* key;             // n_slots: sort key of the slot (class of its head), stochastic slots first
+    uint32_t key_mask;         // bits of the class that take part (0: stochastic slots stay in slot order)
     uint32_t n_slots;
-    unsigned long long* segments;   // device counters: [0] sum of head segments over the live pixels
+    unsigned long long* segments;   // device counters: [0] sum of head segments over the live pixels, [1] stochastic slots
 };
 
 struct ProbeLaunch {           // rt_trace_rays / rt_read_primary_ids / rt_bounce_rays
@@ -157,11 +166,15 @@ cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_head(const HeadLaunch& p, cudaStream_t s);                 // Exact arithmetic, both arms
 cudaError_t launch_trace_tail_strict(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s);
+cudaError_t launch_trace_tail_fast_count(const TraceLaunch& p, cudaStream_t s);   // LBVH scenes only: fills TraceLaunch::work
 cudaError_t launch_combine_chunks(const TraceLaunch& p, cudaStream_t s);
 cudaError_t sort_blocks_by_cost(const uint32_t* cost, uint32_t* cost_sorted, uint32_t* iota, uint32_t* order, uint32_t n,
                                 void* scratch, size_t& scratch_bytes, cudaStream_t s);
-// list = slots partitioned by flag == kHeadStochastic (CUB DevicePartition); *n_stoch on the device
-cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s);
+// list = slots ordered by their 16-bit head key (stable CUB radix sort; `slots` = 0..n_slots-1, made by fill_iota)
+constexpr uint32_t kHeadKeyBits = 16, kHeadKeyOther = 0xFFFFu;
+cudaError_t sort_heads(const uint32_t* key, uint32_t* key_sorted, const uint32_t* slots, uint32_t* list, uint32_t n_slots,
+                       void* scratch, size_t& scratch_bytes, cudaStream_t s);
+cudaError_t fill_iota(uint32_t* v, uint32_t n, cudaStream_t s);
 cudaError_t launch_finalize(const float4* accum, float4* image, int n_pixels, uint32_t spp, cudaStream_t s);
 constexpr int kMaxPeers = 16;
 struct PeerFinalize {          // k_finalize_peers: sum of n_ranks accumulation buffers -> image of rank 0

@@ -197,18 +197,24 @@ __device__ __forceinline__ bool closer(float t, uint32_t id, const Hit& best) {
 // One leaf = one primitive; its 64-byte record (DevBvh::leaves, leaf order = Morton order) holds the test data of the
 // primitive itself, so a leaf visit is one fetch of two sectors next to those of the neighbouring leaves, not an
 // index followed by a dependent fetch from the scene's stream.
-template <class A>
-__device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 d, Hit& best) {
+// Work counters of the instrumented (untimed) LBVH render kernel: the numerator of the roofline of a BVH run is COUNTED
+// work, not the brute-force operation count.
+struct WorkCount { uint32_t nodes, sph, len, tri; };
+template <class A, bool COUNT = false>
+__device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 d, Hit& best, WorkCount* wc = nullptr) {
     const float4 r0 = __ldg(L), r1 = __ldg(L + 1), r2 = __ldg(L + 2), r3 = __ldg(L + 3);
     const uint32_t id = __float_as_uint(r3.x), idx = __float_as_uint(r3.y), kind = id >> 28;
     if (kind == kKindSphere) {
         float t;
+        if (COUNT) ++wc->sph;
         if (sphere_candidate<A>(r0, o, d, t) && closer(t, id, best)) { best.t = t; best.id = id; best.aux = 0u; }
     } else if (kind == kKindLens) {
         float t; uint32_t side;
+        if (COUNT) ++wc->len;
         if (lens_candidate<A>(r0, r1, o, d, t, side) && closer(t, id, best)) { best.t = t; best.id = id; best.aux = side; }
     } else {
         float t, u, v;
+        if (COUNT) ++wc->tri;
         if (dot<A>(mk(r2.y, r2.z, r2.w), d) < 0.0f && hit_triangle<A>(r0, r1, r2, o, d, t, u, v) && closer(t, id, best)) {   // cl:285,295
             best.t = t; best.id = id; best.bu = u; best.bv = v; best.aux = idx;
         }
@@ -651,7 +657,7 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
     const int tile = blockIdx.x * (kTraceThreads / 32) + warp;
     const int x = (tile % tiles_x) * 8 + (lane & 7);
     const int y = (tile / tiles_x) * 4 + (lane >> 3);
-    const bool live = (x < p.W) && (y < p.H);
+    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;   // the region lies inside the frame
 
     const V3 cam_o = mk(p.cam[0], p.cam[1], p.cam[2]);
     const V3 d0 = primary_dir<Exact>(p.cam, x, y, p.W, p.H);   // same primary ray in both arithmetic arms
@@ -716,7 +722,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
     const int tile = blockIdx.x * (kTraceThreads / 32) + warp;
     const int x = (tile % tiles_x) * 8 + (lane & 7);
     const int y = (tile / tiles_x) * 4 + (lane >> 3);
-    const bool live = (x < p.W) && (y < p.H);
+    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;   // the region lies inside the frame
 
     const V3 cam_o = mk(p.cam[0], p.cam[1], p.cam[2]);
     const V3 d0 = primary_dir<Exact>(p.cam, x, y, p.W, p.H);
@@ -840,7 +846,7 @@ __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
     const uint32_t slot = blockIdx.x * kTraceThreads + threadIdx.x;
     int x, y;
     slot_pixel(slot, p.W, x, y);
-    const bool live = slot < p.n_slots && x < p.W && y < p.H;
+    const bool live = slot < p.n_slots && x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;
     uint32_t seg = 0u;
     V3 o = mk(p.cam[0], p.cam[1], p.cam[2]), d = primary_dir<Exact>(p.cam, x, y, p.W, p.H), out = mk(1.0f, 1.0f, 1.0f);
     uint32_t i = 0u, mat_id = 0u;
@@ -886,15 +892,24 @@ __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
     } else if (slot < p.n_slots) {
         p.flag[slot] = kHeadDead;
     }
+    // class of the head for the ordering of the stochastic list: material type, primitive kind and — brute-force scenes
+    // only: with a hierarchy the tile order inside a class is worth more than the primitive — the primitive's low bits
+    const bool stoch = live && flag == kHeadStochastic;
+    if (slot < p.n_slots)
+        p.key[slot] = stoch ? ((((uint32_t)mat_type(mat_id) << 11) | ((h.id >> 28) << 8) | (BVH ? 0u : (h.id & 0xFFu))) & p.key_mask) : kHeadKeyOther;
+    const uint32_t n_st = __popc(__ballot_sync(RT_FULL, stoch));
     seg = __reduce_add_sync(RT_FULL, seg);
-    if ((threadIdx.x & 31) == 0 && seg) atomicAdd(p.segments, (unsigned long long)seg);
+    if ((threadIdx.x & 31) == 0) {
+        if (seg) atomicAdd(p.segments, (unsigned long long)seg);
+        if (n_st) atomicAdd(p.segments + 1, (unsigned long long)n_st);
+    }
 }
 
 // Pixels whose whole path is deterministic: every sample has the colour stored by k_head.
 template <class A>
 __device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) {
     if (j >= p.head.n_slots - p.head.n_stoch) return;
-    const uint32_t slot = __ldg(p.head.list + (p.head.n_slots - 1u - j));
+    const uint32_t slot = __ldg(p.head.list + p.head.n_stoch + j);
     if (__ldg(p.head.flag + slot) != kHeadTerminal) return;
     int x, y;
     slot_pixel(slot, p.W, x, y);
@@ -1002,11 +1017,32 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 // LBVH flavour of trace_tail_body: lanes advance ONE node per trip of the traversal loop (see trace_body_bvh); a lane
 // whose traversal finished waits until `regen` lanes wait, then the waiting lanes close their path on a miss / light,
 // or shade the hit and start the bounced ray; finished paths restart from the stored head.
-template <class A>
+//   * Box test per node: the distance-proportional inflation (slab<true>) is needed only where a sphere or a lens can be
+//     hit (BvhNode::flags, set by the builder); the fast arm tests triangle-only nodes with the plain slab.  The strict arm
+//     keeps the inflated test everywhere (its equality with brute force is what tests/test_gpu_bvh.py pins).
+//   * Leaves: a trip tests at most two leaves per lane through ONE copy of the leaf code (lanes whose first or second
+//     child is a leaf run it together).
+//   * Traversal stack: the first RT_BVH_SSTACK levels in shared memory ([level][thread], conflict free), the rest —
+//     practically never used — in local memory.
+#ifndef RT_BVH_SSTACK
+#define RT_BVH_SSTACK 24
+#endif
+#ifndef RT_BVH_FLAG_SLAB
+#define RT_BVH_FLAG_SLAB 1
+#endif
+template <class A, bool COUNT>
 __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     if (blockIdx.x >= p.tail_blocks) { terminal_body<A>(p, (blockIdx.x - p.tail_blocks) * kTraceThreads + threadIdx.x); return; }
     __shared__ float4 hs_all[4 * kTraceThreads];
     float4* hs = hs_all + threadIdx.x;
+#if RT_BVH_SSTACK > 0
+    __shared__ int sstack_all[RT_BVH_SSTACK * kTraceThreads];
+    int* sst = sstack_all + threadIdx.x;
+    int lst[kBvhStack - RT_BVH_SSTACK];
+#else
+    int* sst = nullptr;
+    int lst[kBvhStack];
+#endif
     const float4* S = p.sc.stream;
     const uint32_t lane = threadIdx.x & 31u;
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
@@ -1028,16 +1064,23 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
     };
     uint32_t queries = 0u;
+    WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false, has_ray = false, have_result = false, exhausted = false;
+    auto push = [&](int v) {
+        if (sp < RT_BVH_SSTACK) sst[sp * kTraceThreads] = v;
+        else if (sp < kBvhStack) lst[sp - RT_BVH_SSTACK] = v;
+        else return;
+        ++sp;
+    };
+    auto pop = [&]() { --sp; return sp < RT_BVH_SSTACK ? sst[sp * kTraceThreads] : lst[sp - RT_BVH_SSTACK]; };
     auto start_ray = [&]() {
         h.t = RT_T_MAX; h.id = kIdMiss; h.bu = 0.0f; h.bv = 0.0f; h.aux = 0u;
         hit_planes<A>(p.sc, S, o, d, h);
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
-        if (traversing && node < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~node), o, d, h); traversing = false; }
+        if (traversing && node < 0) { bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~node), o, d, h, &wc); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
         have_result = true;
     };
@@ -1099,16 +1142,27 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
-                bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
-                if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
-                if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
+                bool h0, h1;
+                if (COUNT) ++wc.nodes;
+                if (RT_BVH_FLAG_SLAB && !A::kExact && __float_as_uint(n2.w) == 0u) {
+                    h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
+                } else {
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1);
+                }
+                int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
+                if (l0 == 0) { l0 = l1; l1 = 0; }
+                while (l0 != 0) {
+                    bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~l0), o, d, h, &wc);
+                    l0 = l1; l1 = 0;
+                }
+                h0 = h0 && c0 >= 0; h1 = h1 && c1 >= 0;
                 if (h0 && h1) {
                     const bool first0 = t0 <= t1;
-                    if (sp < kBvhStack) stack[sp++] = first0 ? c1 : c0;
+                    push(first0 ? c1 : c0);
                     node = first0 ? c0 : c1;
                 } else if (h0) node = c0;
                 else if (h1) node = c1;
-                else if (sp > 0) node = stack[--sp];
+                else if (sp > 0) node = pop();
                 else traversing = false;
             }
             const unsigned trav = __ballot_sync(RT_FULL, traversing);
@@ -1118,6 +1172,14 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     }
     queries = __reduce_add_sync(RT_FULL, queries);
     if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
+    if (COUNT) {
+        const uint32_t a = __reduce_add_sync(RT_FULL, wc.nodes), b = __reduce_add_sync(RT_FULL, wc.sph),
+                       c = __reduce_add_sync(RT_FULL, wc.len), e = __reduce_add_sync(RT_FULL, wc.tri);
+        if (lane == 0u && p.work) {
+            atomicAdd(p.work + 0, (unsigned long long)a); atomicAdd(p.work + 1, (unsigned long long)b);
+            atomicAdd(p.work + 2, (unsigned long long)c); atomicAdd(p.work + 3, (unsigned long long)e);
+        }
+    }
 }
 
 // Nearest hit of arbitrary rays (rays6 != nullptr) or of the primary rays of the frame; same code path as the

@@ -21,7 +21,10 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_tra
 #define RT_BVH_MIN_BLOCKS 8
 #endif
 extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_BVH_MIN_BLOCKS) k_trace_tail_fast_bvh(const __grid_constant__ TraceLaunch p) {
-    trace_tail_bvh_body<Fused>(p);
+    trace_tail_bvh_body<Fused, false>(p);
+}
+extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_BVH_MIN_BLOCKS) k_trace_tail_fast_bvh_count(const __grid_constant__ TraceLaunch p) {
+    trace_tail_bvh_body<Fused, true>(p);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_fast(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];
@@ -44,6 +47,9 @@ cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s) {
 cudaError_t launch_trace_tail_fast(const TraceLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_tail_bvh(k_trace_tail_fast_bvh, p, s)
                           : launch_staged(k_trace_tail_fast, p, tail_work_items(p), s, false, kHeadStateBytes);
+}
+cudaError_t launch_trace_tail_fast_count(const TraceLaunch& p, cudaStream_t s) {
+    return p.bvh.n_leaves ? launch_tail_bvh(k_trace_tail_fast_bvh_count, p, s) : cudaErrorInvalidValue;
 }
 cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s) {
     return p.bvh.n_leaves ? launch_staged(k_probe_hits_fast_bvh, p, p.n, s, true) : launch_staged(k_probe_hits_fast, p, p.n, s);

@@ -23,7 +23,7 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_strict(
     trace_tail_body<Exact>(p, smem);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_trace_tail_strict_bvh(const __grid_constant__ TraceLaunch p) {
-    trace_tail_bvh_body<Exact>(p);
+    trace_tail_bvh_body<Exact, false>(p);
 }
 extern "C" __global__ void __launch_bounds__(kTraceThreads) k_probe_hits_strict(const __grid_constant__ ProbeLaunch p) {
     extern __shared__ float4 smem[];

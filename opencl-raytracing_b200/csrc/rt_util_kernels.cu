@@ -3,7 +3,6 @@
 #include "rt_device.h"
 
 #include <cub/cub.cuh>
-#include <thrust/iterator/counting_iterator.h>
 
 namespace rtb {
 
@@ -77,14 +76,16 @@ cudaError_t sort_blocks_by_cost(const uint32_t* cost, uint32_t* cost_sorted, uin
     return cub::DeviceRadixSort::SortPairsDescending(scratch, scratch_bytes, cost, cost_sorted, iota, order, (int)n, 0, 32, s);
 }
 
-// Slots with a stochastic path head to the front of `list` (in slot order), all others to the back (reversed).
-struct IsStochastic {
-    const uint8_t* flag;
-    __device__ bool operator()(uint32_t slot) const { return flag[slot] == kHeadStochastic; }
-};
-cudaError_t partition_heads(const uint8_t* flag, uint32_t n_slots, uint32_t* list, uint32_t* d_n_stoch, void* scratch, size_t& scratch_bytes, cudaStream_t s) {
-    thrust::counting_iterator<uint32_t> slots(0u);
-    return cub::DevicePartition::If(scratch, scratch_bytes, slots, list, d_n_stoch, (int)n_slots, IsStochastic{flag}, s);
+// Slots ordered by the class of their path head (HeadLaunch::key): a stable radix sort over the 16 key bits keeps the
+// slot (= tile) order inside a class; the stochastic classes come first, everything else has key kHeadKeyOther.
+cudaError_t sort_heads(const uint32_t* key, uint32_t* key_sorted, const uint32_t* slots, uint32_t* list, uint32_t n_slots,
+                       void* scratch, size_t& scratch_bytes, cudaStream_t s) {
+    return cub::DeviceRadixSort::SortPairs(scratch, scratch_bytes, key, key_sorted, slots, list, (int)n_slots, 0, (int)kHeadKeyBits, s);
+}
+cudaError_t fill_iota(uint32_t* v, uint32_t n, cudaStream_t s) {
+    if (!n) return cudaSuccess;
+    k_iota<<<(n + 255u) / 256u, 256, 0, s>>>(v, n);
+    return cudaGetLastError();
 }
 
 // 16 independent FFMA chains per thread; 2 flops / 1 issue slot per FFMA per lane.

@@ -67,7 +67,7 @@ def lib():
         "rt_create": [ci, ci, ci, C.POINTER(vp)], "rt_destroy": [vp], "rt_set_stream": [vp, vp],
         "rt_upload_scene": [vp, C.POINTER(SceneDesc)], "rt_upload_textures": [vp, vp, ci, ci, ci],
         "rt_make_random_table": [u32, vp], "rt_set_random_table": [vp, vp, u32],
-        "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
+        "rt_set_region": [vp, ci, ci, ci, ci], "rt_set_work_counting": [vp, ci], "rt_get_work_counts": [vp, vp], "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
         "rt_render": [vp, vp], "rt_render_again": [vp, vp], "rt_render_samples": [vp, vp, u32, u32, u32],
         "rt_clear_accum": [vp], "rt_invalidate_caches": [vp], "rt_finalize": [vp, u32], "rt_read_image": [vp, vp], "rt_read_accum": [vp, vp],
         "rt_read_primary_ids": [vp, vp, vp, vp], "rt_restore_image": [vp, vp, u32], "rt_restore_accum": [vp, vp, u32], "rt_get_stats": [vp, C.POINTER(Stats)],
@@ -222,6 +222,20 @@ class Context:
                    accel=ACCEL_AUTO, path_head=HEAD_ON):
         p = Params(max_depth, rng_mode, seed, arith, mesh_mode, accel, path_head)
         _check(self.L.rt_set_params(self.h, C.byref(p)))
+
+    def set_region(self, x0=0, y0=0, w=0, h=0):
+        """Render only pixels [x0, x0+w) x [y0, y0+h); w <= 0 restores the whole frame."""
+        _check(self.L.rt_set_region(self.h, x0, y0, w, h))
+
+    def set_work_counting(self, on):
+        _check(self.L.rt_set_work_counting(self.h, 1 if on else 0))
+
+    def work_counts(self):
+        """-> dict of the counted work of the last LBVH render made while counting was on."""
+        w = np.zeros(8, np.uint64)
+        _check(self.L.rt_get_work_counts(self.h, w.ctypes.data))
+        return dict(node_visits=int(w[0]), sphere_tests=int(w[1]), lens_tests=int(w[2]), triangle_tests=int(w[3]),
+                    plane_tests=int(w[4]), queries=int(w[5]))
 
     @staticmethod
     def _cam(cam):

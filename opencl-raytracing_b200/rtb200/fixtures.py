@@ -1,5 +1,5 @@
-"""rtb200.fixtures — load a packed scene fixture (tests/golden/scene_*.npz) into the arrays rt_upload_scene
-takes, and prepare the inputs a host application would prepare: float textures (stb_image's LDR->float law,
+"""rtb200.fixtures — load a packed scene (rtb200/data/scene_*.npz: package data, the parsed default scene of the reference
+and the C3 cube scene in the reference's host layouts) into the arrays rt_upload_scene takes, and prepare the inputs a host application would prepare: float textures (stb_image's LDR->float law,
 as src/scene.cpp:158 obtains them), the random table and the Camera::transferData() vector."""
 from __future__ import annotations
 
@@ -8,8 +8,7 @@ import os
 
 import numpy as np
 
-REPO = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-GOLDEN = os.path.join(REPO, "tests", "golden")
+DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
 ARRAY_NAMES = ("materials", "spheres", "planes", "lenses", "vertices", "uvs", "indices", "meshes", "models")
 ITEM_BYTES = dict(materials=48, spheres=32, planes=48, lenses=64, vertices=16, uvs=8, indices=4, meshes=16, models=12)
 
@@ -44,11 +43,11 @@ def textures_to_float(rgba8):
 
 
 def default_scene():
-    return load_scene_npz(os.path.join(GOLDEN, "scene_default.npz"))
+    return load_scene_npz(os.path.join(DATA, "scene_default.npz"))
 
 
 def c3_scene():
-    return load_scene_npz(os.path.join(GOLDEN, "scene_c3.npz"))
+    return load_scene_npz(os.path.join(DATA, "scene_c3.npz"))
 
 
 def camera(fov_deg, aspect, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):

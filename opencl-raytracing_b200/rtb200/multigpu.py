@@ -61,3 +61,35 @@ class PeerFinalize:
 
     def close(self):
         self.ctx.close_peers()
+
+
+def split_image_check(ctx, cam, spp, world, rank, finalize_split, group=None):
+    """Correctness of the real multi-process path: the `world`-rank picture (every rank renders its global sample range
+    into its linear-sum buffer, finalize_split(spp) = the exchange step: PeerFinalize.finalize or reduce_to_rank0 +
+    rt_finalize on rank 0) against the same job rendered by rank 0 alone.  The RNG is keyed by global sample indices, so
+    the two differ by float summation order only.  Collective: every rank calls it; rank 0 gets
+    {"max_abs", "spp", "ok"}, the others None."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from . import ACCUM_SUM
+    first, n = sample_range(spp, world, rank)
+    ctx.clear_accum()
+    ctx.render_samples(cam, first, n, ACCUM_SUM)
+    finalize_split(spp)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier(group=group)
+    out = None
+    if rank == 0:
+        split = ctx.read_image().copy()
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, spp, ACCUM_SUM)
+        ctx.finalize(spp)
+        single = ctx.read_image()
+        max_abs = float(np.abs(split[..., :3] - single[..., :3]).max())
+        out = {"max_abs": max_abs, "spp": int(spp), "tolerance": 2e-6,
+               "ok": bool(max_abs <= 2e-6 and np.all(split[..., 3] == 1.0) and float(single[..., :3].max()) > 0.1)}
+    if world > 1:
+        dist.barrier(group=group)
+    return out

@@ -146,6 +146,10 @@ class PortOracle:
         L.orc_render.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(OrcParams),
                                  C.POINTER(C.c_uint64)]
+        L.orc_render_window.restype = C.c_double
+        L.orc_render_window.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
+                                        C.POINTER(OrcParams), C.POINTER(C.c_uint64)]
         L.orc_intersect.restype = C.c_int
         L.orc_intersect.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(OrcHit)]
         L.orc_primary_ids.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_void_p,
@@ -184,6 +188,19 @@ class PortOracle:
         secs = self.lib.orc_render(C.byref(desc), tex.ctypes.data, tex.shape[2], tex.shape[1], tex.shape[0],
                                    cam.ctypes.data, tp, image.ctypes.data, W, H, first, n, C.byref(prm),
                                    C.byref(rays))
+        return image, rays.value, secs
+
+    def render_window(self, desc, tex, cam, table, W, H, x0, y0, w, h, first, n, prm=None):
+        """Pixels [x0, x0+w) x [y0, y0+h) of the W x H frame -> (image [h, w, 4], rays, seconds)."""
+        tex = _tex(tex)
+        prm = prm or self.params()
+        image = np.zeros((h, w, 4), dtype=np.float32)
+        rays = C.c_uint64(0)
+        cam = np.ascontiguousarray(cam, dtype=np.float32)
+        tp = table.ctypes.data if table is not None else None
+        secs = self.lib.orc_render_window(C.byref(desc), tex.ctypes.data, tex.shape[2], tex.shape[1], tex.shape[0],
+                                          cam.ctypes.data, tp, image.ctypes.data, W, H, x0, y0, w, h, first, n,
+                                          C.byref(prm), C.byref(rays))
         return image, rays.value, secs
 
     def intersect(self, desc, origin, direction, mesh_mode=MESH_FIRST_FRONT):

@@ -462,6 +462,7 @@ typedef struct {
     const float* cam;
     float* image;
     int W, H;
+    int x0, y0, w, h;          /* window of the W x H frame that is rendered; image is w x h */
     uint32_t first, n;
     int next_row;
     uint64_t rays;
@@ -475,14 +476,14 @@ static void* worker(void* arg) {
         pthread_mutex_lock(&j->mu);
         int y0 = j->next_row; j->next_row += 2;
         pthread_mutex_unlock(&j->mu);
-        if (y0 >= j->H) break;
-        int y1 = y0 + 2 < j->H ? y0 + 2 : j->H;
+        if (y0 >= j->y0 + j->h) break;
+        int y1 = y0 + 2 < j->y0 + j->h ? y0 + 2 : j->y0 + j->h;
         for (int y = y0; y < y1; y++)
-            for (int x = 0; x < j->W; x++) {
+            for (int x = j->x0; x < j->x0 + j->w; x++) {
                 ctx_t c = j->base;
                 c.sc = &j->sc; c.tex = &j->tex; c.gx = (uint32_t)x; c.gy = (uint32_t)y; c.W = (uint32_t)j->W;
                 v3 o = vld(j->cam), d0 = primary_dir(j->cam, x, y, j->W, j->H);
-                float* px = j->image + 4 * ((size_t)y * j->W + x);
+                float* px = j->image + 4 * ((size_t)(y - j->y0) * j->w + (x - j->x0));
                 for (uint32_t k = j->first; k < j->first + j->n; k++) {
                     v3 col = path_radiance(&c, o, d0, k, &rays);
                     if (c.prm->accum_mode == ORC_ACCUM_SUM) {
@@ -509,12 +510,21 @@ static void* worker(void* arg) {
 double orc_render(const orc_scene_desc* scene, const float* tex, int tw, int th, int tl, const float* cam12,
                   const float* table, float* image, int W, int H, uint32_t first, uint32_t n,
                   const orc_params* prm, uint64_t* rays) {
+    return orc_render_window(scene, tex, tw, th, tl, cam12, table, image, W, H, 0, 0, W, H, first, n, prm, rays);
+}
+
+/* Work-items (x, y) in [x0, x0+w) x [y0, y0+h) of the W x H NDRange only (same s = x/W, t = y/H and the same
+ * per-pixel RNG keys as in the full frame); image is the w x h window, row 0 = y0. */
+double orc_render_window(const orc_scene_desc* scene, const float* tex, int tw, int th, int tl, const float* cam12,
+                         const float* table, float* image, int W, int H, int x0, int y0, int w, int h,
+                         uint32_t first, uint32_t n, const orc_params* prm, uint64_t* rays) {
     job_t j;
     memset(&j, 0, sizeof j);
     j.sc = scene_from_desc(scene);
     j.tex.data = tex; j.tex.w = tw; j.tex.h = th; j.tex.layers = tl;
     j.base.table = table; j.base.prm = prm;
     j.cam = cam12; j.image = image; j.W = W; j.H = H; j.first = first; j.n = n;
+    j.x0 = x0; j.y0 = y0; j.w = w; j.h = h; j.next_row = y0;
     pthread_mutex_init(&j.mu, 0);
     int nt = prm->threads < 1 ? 1 : (prm->threads > 256 ? 256 : prm->threads);
     pthread_t th_[256];

@@ -61,6 +61,11 @@ double orc_render(const orc_scene_desc* scene, const float* tex, int tw, int th,
                   const float* table, float* image, int W, int H, uint32_t first, uint32_t n,
                   const orc_params* prm, uint64_t* rays);
 
+/* The same for the work-items of a window [x0, x0+w) x [y0, y0+h) of the W x H frame; image is w x h. */
+double orc_render_window(const orc_scene_desc* scene, const float* tex, int tw, int th, int tl, const float* cam12,
+                         const float* table, float* image, int W, int H, int x0, int y0, int w, int h,
+                         uint32_t first, uint32_t n, const orc_params* prm, uint64_t* rays);
+
 int orc_intersect(const orc_scene_desc* scene, const float* origin, const float* dir, uint32_t mesh_mode,
                   orc_hit* out);
 

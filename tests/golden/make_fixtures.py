@@ -5,8 +5,8 @@ The reference ships no tests, golden vectors or fixtures for this path (SURVEY.m
 are outputs of the reference's own kernel text compiled as C++ (oracle/_ref/libref_strict.so) on inputs
 prepared by oracle/scene_py.py from the reference's assets:
 
-  scene_default.npz   assets/scenes/scene.scene parsed into the reference's host AoS arrays + RGBA8 textures
-  scene_c3.npz        tests/golden/scenes/c3_cube.scene (reference cube meshes + die textures), config C3
+  (rtb200/data/) scene_default.npz   assets/scenes/scene.scene parsed into the reference's host AoS arrays + RGBA8 textures
+  (rtb200/data/) scene_c3.npz        tests/golden/scenes/c3_cube.scene (reference cube meshes + die textures), config C3
   golden_default.npz  reference outputs on scene_default: 160x120 image after 1 and 4 samples (depth 30),
                       primary ids/t at 160x120 and ids at 800x600, ray counts, table checksum; single-bounce
                       vectors (ray in -> ray out, throughput) for 256 recorded rays
@@ -25,6 +25,7 @@ import scene_py as sp  # noqa: E402
 
 REF = "/root/reference"
 HERE = os.path.dirname(os.path.abspath(__file__))
+DATA = os.path.join(os.path.dirname(os.path.dirname(HERE)), "opencl-raytracing_b200", "rtb200", "data")   # package data of rtb200
 TABLE_SEED = 12345
 
 
@@ -97,7 +98,7 @@ def main():
     sc = sp.parse_scene_file(os.path.join(REF, "assets/scenes/scene.scene"), root=REF)
     sc.load_textures(resolver)
     arr = sc.arrays()
-    np.savez_compressed(os.path.join(HERE, "scene_default.npz"), **pack(arr))
+    np.savez_compressed(os.path.join(DATA, "scene_default.npz"), **pack(arr))
     tex = sp.texture_from_rgba8(arr["textures_rgba8"])
     g = golden(R, arr, tex, table, 160, 120, big=(800, 600))
     g.update(table_seed=TABLE_SEED, table_sha256=tsum)
@@ -106,13 +107,13 @@ def main():
     sc3 = sp.parse_scene_file(os.path.join(HERE, "scenes/c3_cube.scene"), root=REF)
     sc3.load_textures(resolver)
     arr3 = sc3.arrays()
-    np.savez_compressed(os.path.join(HERE, "scene_c3.npz"), **pack(arr3))
+    np.savez_compressed(os.path.join(DATA, "scene_c3.npz"), **pack(arr3))
     tex3 = sp.texture_from_rgba8(arr3["textures_rgba8"])
     g3 = golden(R, arr3, tex3, table, 160, 90, big=(480, 270))
     g3.update(table_seed=TABLE_SEED, table_sha256=tsum)
     np.savez_compressed(os.path.join(HERE, "golden_c3.npz"), **g3)
-    for f in ("scene_default.npz", "golden_default.npz", "scene_c3.npz", "golden_c3.npz"):
-        print(f, os.path.getsize(os.path.join(HERE, f)))
+    for d_, f in ((DATA, "scene_default.npz"), (HERE, "golden_default.npz"), (DATA, "scene_c3.npz"), (HERE, "golden_c3.npz")):
+        print(f, os.path.getsize(os.path.join(d_, f)))
 
 
 if __name__ == "__main__":

@@ -4,7 +4,7 @@ ctypes binding of include/rt_capi.h) and is checked against the oracle on the sa
 Bars (stated here, repeated in DESIGN.md):
   STRICT arithmetic  bit-exact: image bits, ray counts, primary ids and t, single-bounce outputs.
                      (A dielectric pow() rounding flip is possible with probability ~1e-8 per bounce; the
-                      image tests allow <= 3 differing pixels per frame for that single reason.)
+                      image tests allow <= 1 differing pixel per frame for that single reason and print the observed count.)
   FAST arithmetic    identical primary-hit ids; single-bounce outputs within 2e-4 absolute for
                      non-chaotic (non-table-hashed) results; image RMSE(gamma) vs oracle <= 0.03 at 16 spp
                      (the reference's own FMA-on/off difference is 0.022) and mean difference <= 2e-3.
@@ -40,7 +40,12 @@ def make_ctx(rt, scenes, name, W, H, table, **params):
 
 
 def n_diff_pixels(a, b):
-    return int((bits(a[..., :3]) != bits(b[..., :3])).any(-1).sum())
+    """Pixels whose bits differ; the observed count is printed (pytest -s / the captured output of a failure) so that the
+    allowance of ONE pixel per frame — a powf double-rounding flip of the Schlick term, p ~ 1e-8 per dielectric bounce —
+    cannot hide anything: the expected count at 480 k pixels x 16 spp is 0.05."""
+    n = int((bits(a[..., :3]) != bits(b[..., :3])).any(-1).sum())
+    print("differing pixels: %d of %d" % (n, a.shape[0] * a.shape[1]))
+    return n
 
 
 @pytest.mark.parametrize("name,W,H,spp,depth", [("default", 800, 600, 16, 8), ("default", 320, 200, 8, 30),
@@ -59,7 +64,7 @@ def test_strict_image_bit_exact(rt, port, scenes, table, name, W, H, spp, depth)
             ctx.render_again(cam)
             rays += ctx.stats().rays_last
         got = ctx.read_image()
-        assert n_diff_pixels(got, want) <= 3
+        assert n_diff_pixels(got, want) <= 1
         assert abs(int(rays) - int(rays_want)) <= 60
         assert ctx.stats().rays_total == rays and ctx.stats().samples_done == spp
         assert np.all(got[..., 3] == 1.0)
@@ -85,12 +90,12 @@ def test_golden_fixture_images(rt, scenes, golden, table, name):
         assert abs(int(ctx.stats().rays_last) - int(g["rays_1spp"])) <= 20
         for _ in range(3):
             ctx.render_again(cam)
-        assert n_diff_pixels(ctx.read_image(), g["image_4spp"]) <= 2
+        assert n_diff_pixels(ctx.read_image(), g["image_4spp"]) <= 1
         ids, ts = ctx.primary_ids(cam)
         assert np.array_equal(ids, g["ids"]) and np.array_equal(bits(ts), bits(g["ts"]))
         ctx.set_params(max_depth=8, arith=rt.ARITH_STRICT)
         ctx.render_samples(cam, 0, 4, rt.ACCUM_REFERENCE)
-        assert n_diff_pixels(ctx.read_image(), g["image_4spp_depth8"]) <= 2
+        assert n_diff_pixels(ctx.read_image(), g["image_4spp_depth8"]) <= 1
 
 
 @pytest.mark.parametrize("arith", ["strict", "fast"])
@@ -172,7 +177,7 @@ def test_counter_rng_strict_bit_exact_and_same_law(rt, port, scenes, table):
     with make_ctx(rt, scenes, "default", W, H, table, max_depth=30, arith=rt.ARITH_STRICT, rng_mode=rt.RNG_COUNTER, seed=77) as ctx:
         ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
         got = ctx.read_image()
-        assert n_diff_pixels(got, want) <= 3
+        assert n_diff_pixels(got, want) <= 1
         assert abs(int(ctx.stats().rays_last) - int(rays_want)) <= 60
         ctx.set_params(max_depth=30, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER, seed=78)
         ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
@@ -200,7 +205,7 @@ def test_counter_table_rng_strict_bit_exact_and_same_law(rt, port, scenes, table
     with make_ctx(rt, scenes, "default", W, H, table, max_depth=30, arith=rt.ARITH_STRICT, rng_mode=rt.RNG_COUNTER_TABLE, seed=77) as ctx:
         ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
         got = ctx.read_image()
-        assert n_diff_pixels(got, want) <= 3
+        assert n_diff_pixels(got, want) <= 1
         assert abs(int(ctx.stats().rays_last) - int(rays_want)) <= 60
         ctx.set_params(max_depth=30, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=78)
         ctx.render_samples(cam, 0, spp, rt.ACCUM_REFERENCE)
