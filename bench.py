@@ -44,9 +44,9 @@ CONFIGS = {
                workload="C2: default scene (8 spheres, 1 plane, 1 lens, 2 textured cubes = 24 triangles), 1920x1080, 1024 spp, max depth 30"),
     "c3": dict(W=1920, H=1080, spp=4096, depth=30, mesh_mode=0, scene="c3", slots=738.0, short_spp=1024,
                workload="C3: reference cube meshes (textured) + diffuse/dielectric/reflective spheres, 1920x1080, 4096 spp, max depth 30"),
-    "c4": dict(W=3840, H=2160, spp=64, depth=30, mesh_mode=1, scene="c4", slots=None, short_spp=32,
+    "c4": dict(W=3840, H=2160, spp=64, depth=30, mesh_mode=1, scene="c4", slots=None, short_spp=256,
                workload="C4: synthetic closed mesh of 1 310 720 triangles + 1001 spheres + floor plane, 3840x2160, GPU-built LBVH, max depth 30"),
-    "c5": dict(W=3840, H=2160, spp=64, depth=16, mesh_mode=1, scene="c5", slots=None, short_spp=32,
+    "c5": dict(W=3840, H=2160, spp=64, depth=16, mesh_mode=1, scene="c5", slots=None, short_spp=256,
                workload="C5: 100 001 mixed-material spheres + floor plane, 3840x2160, GPU-built LBVH, max depth 16"),
 }
 SLOTS_SOURCE = {
@@ -85,9 +85,11 @@ def parse():
     ap.add_argument("--arith", default="fast", choices=["fast", "strict"])
     ap.add_argument("--rng", default="counter_table", choices=["counter_table", "counter", "table"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--reduce", default="fused", choices=["fused", "nccl"],
+    ap.add_argument("--reduce", default="fused", choices=["fused", "fused_nccl_barriers", "nccl"],
                     help="N > 1: fused = every rank reduces+finalizes its rows out of the peers' buffers (CUDA IPC over NVLink, "
-                         "rt_finalize_peers); nccl = one torch.distributed reduce to rank 0 + rt_finalize")
+                         "rt_finalize_peers_barrier_async: the ranks meet through arrival words in peer memory, no collective call); "
+                         "fused_nccl_barriers = the same kernel between two NCCL all-reduces of a scalar (round 1); "
+                         "nccl = one torch.distributed reduce to rank 0 + rt_finalize")
     ap.add_argument("--no-heads", action="store_true", help="RT_HEAD_OFF: trace every segment of every sample (A/B of the path-head memoisation)")
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS),
                     help="BASELINE.json configs; the driver's default (and the headline) is c2")
@@ -293,13 +295,13 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     ctx.upload_textures(tex); ctx.upload_scene(arr); ctx.set_random_table(table)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    fused = world > 1 and a.reduce == "fused"
+    fused = world > 1 and a.reduce != "nccl"
     accum = None
     if not fused:          # torch-owned buffer (what dist.reduce needs); the fused path exports the context's own buffer
         accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
         ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
-    peers = PeerFinalize(ctx, stream_ordered=True) if fused else None
+    peers = PeerFinalize(ctx, stream_ordered=True, device_barrier=(a.reduce == "fused")) if fused else None
     first, n_mine = sample_range(spp, world, rank)
 
     def exchange(total_spp):
@@ -406,6 +408,34 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         e2e_s, e2e_rays = m[0].item(), s[1].item()
     e2e_value = e2e_rays / e2e_s / 1e6
 
+    # ---- the reference's own call pattern through the C ABI (main.cpp:91-95 -> src/raytracer.cpp:127-165): render() once, then
+    # renderAgain() per sample, the image read at the end.  rt_render / rt_render_again record the samples and one launch renders
+    # them when the image is read (bit-identical to one launch per call); RTB200_EAGER=1 is the reference's schedule, one launch
+    # and one host round trip per sample, timed on fewer samples.
+    api = None
+    if world == 1 and with_cpu_baseline is not None and cfg["name"] in ("c1", "c2"):
+        def api_run(n_samples):
+            ctx.invalidate_caches()
+            t_a = time.perf_counter()
+            ctx.render(cam)
+            for _ in range(n_samples - 1):
+                ctx.render_again(cam)
+            ctx.read_image(img_host)
+            dt = time.perf_counter() - t_a
+            return ctx.stats().rays_total / dt / 1e6, dt
+        api_run(min(spp, 64))
+        v_def, s_def = api_run(spp)
+        os.environ["RTB200_EAGER"] = "1"
+        n_eager = min(spp, 128)
+        api_run(8)
+        v_eag, s_eag = api_run(n_eager)
+        del os.environ["RTB200_EAGER"]
+        api = {"value": round(v_def, 1), "unit": "Mrays/s", "samples": spp, "seconds": round(s_def, 4),
+               "what": "rt_render + %d x rt_render_again + rt_read_image (host wall clock, image copied to the host): what RayTracer::render() / "
+                       "renderAgain() of include/raytracer.h call; the recorded samples are rendered by one launch when the image is read" % (spp - 1),
+               "eager": {"value": round(v_eag, 1), "samples": n_eager, "us_per_sample": round(1e6 * s_eag / n_eager, 1),
+                         "what": "RTB200_EAGER=1: one launch + one host synchronisation per sample, the reference's schedule (src/raytracer.cpp:137-140,158-161)"}}
+
     out = None
     if rank == 0:
         k_ms = sum(kernel_ms) / len(kernel_ms)
@@ -456,7 +486,8 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
             "steps": steps, "warmup": warmup, "ms_per_step": round(elapsed_ms / steps, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_block(cfg, spp_total=spp, spp_per_gpu=n_mine, arith=a.arith, rng=a.rng,
-                                   parallelism=("spp-split x%d + %s" % (world, "fused peer-memory reduce+finalize (rt_finalize_peers)" if fused else "1 NCCL reduce"))
+                                   parallelism=("spp-split x%d + %s" % (world, ("fused peer-memory reduce+finalize, device-side rank barrier (rt_finalize_peers_barrier_async)" if a.reduce == "fused"
+                                                                              else "fused peer-memory reduce+finalize between two NCCL barriers") if fused else "1 NCCL reduce"))
                                    if world > 1 else "single GPU",
                                    rays_per_step=int(rays_total / steps), path_heads=not a.no_heads, bvh_nodes=int(ctx.stats().bvh_nodes),
                                    queries=int(queries_launch),
@@ -471,6 +502,8 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         }
         if check is not None:
             out["multi_gpu_check"] = check
+        if api is not None:
+            out["api_path"] = api
         if world == 1 and with_cpu_baseline:
             spp_step, window = reference_sampling(cfg)
             reps = {"c1": 2, "c2": 4, "c3": 3, "c4": 1, "c5": 2}[cfg["name"]]
@@ -519,7 +552,7 @@ def main_b200(a, cfg):
                                with_cpu_baseline=not a.no_cpu_baseline)
             if e is not None:
                 extras.append({k: e[k] for k in ("value", "value_executed", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "config", "e2e",
-                                                 "gpu_launches", "roofline", "multi_gpu_check", "cpu_baseline") if k in e})
+                                                 "gpu_launches", "roofline", "multi_gpu_check", "cpu_baseline", "api_path") if k in e})
     if rank == 0:
         if extras:
             out["extra_configs"] = extras

@@ -109,7 +109,13 @@ int rt_set_region(rt_ctx* ctx, int x0, int y0, int w, int h);
 
 /* RayTracer::render (src/raytracer.cpp:127-144): sample_counter = 0, one sample, overwrites the image. */
 int rt_render(rt_ctx* ctx, const float camera[12]);
-/* RayTracer::renderAgain (src/raytracer.cpp:146-165): ++sample_counter, one more sample, running mean. */
+/* RayTracer::renderAgain (src/raytracer.cpp:146-165): ++sample_counter, one more sample, running mean.
+ * Execution of rt_render / rt_render_again is DEFERRED: the calls validate their arguments and record the sample;
+ * consecutive samples with one camera are rendered by a single launch as soon as anything observes the image or the
+ * statistics or changes state they depend on (rt_read_image, rt_get_stats, rt_image_device_ptr, uploads, rt_set_params,
+ * ...), or after 4096 recorded samples.  The image every observer sees is bit-identical to one launch per call — the
+ * reference's own schedule, one launch + queue.finish() per sample (src/raytracer.cpp:137-140,158-161), which the
+ * environment variable RTB200_EAGER=1 restores.  rt_stats.rays_last / ms_last then describe the last launch. */
 int rt_render_again(rt_ctx* ctx, const float camera[12]);
 /* n_samples consecutive samples [first, first+n) in ONE launch.  accum_mode RT_ACCUM_REFERENCE continues the
  * reference's sqrt(mean) chain in the image (first == 0 restarts it; bit-identical to render + renderAgain
@@ -156,6 +162,14 @@ int rt_ipc_open_peers(rt_ctx* ctx, int n_ranks, int my_rank, const void* accum_h
 int rt_set_peers_direct(rt_ctx* ctx, int n_ranks, int my_rank, void* const* accum_ptrs, void* image_rank0);
 int rt_finalize_peers(rt_ctx* ctx, uint32_t total_spp);
 int rt_finalize_peers_async(rt_ctx* ctx, uint32_t total_spp);   /* enqueue only: ordered on the context's stream */
+/* The same with the two rank synchronisations done ON THE DEVICE: arrival words in peer memory (they live behind every
+ * accumulation buffer, so the IPC mapping of rt_ipc_open_peers already covers them) released and awaited by a one-warp
+ * kernel before ("every rank's render is complete") and after ("every slice of the image is written") the fused
+ * reduce + finalize.  No collective call, no host round trip: the whole exchange is three launches on the context's
+ * stream.  All ranks must call it the same number of times.  rt_peer_barrier_status reports whether a wait ever gave up
+ * (a rank that never arrived; ~10 s) instead of hanging the device. */
+int rt_finalize_peers_barrier_async(rt_ctx* ctx, uint32_t total_spp);
+int rt_peer_barrier_status(rt_ctx* ctx, int* timed_out);
 int rt_close_peers(rt_ctx* ctx);
 
 /* Probes used by the parity tests: nearest hit of arbitrary rays, and one bounce of the path loop.

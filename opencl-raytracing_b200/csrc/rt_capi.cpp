@@ -139,6 +139,14 @@ struct rt_ctx {
     void* peer_image0 = nullptr;
     bool peer_opened[kMaxPeers] = {false};   // accum pointers obtained from cudaIpcOpenMemHandle
     bool peer_image_opened = false;
+    bool peer_flags_ok = false;               // peers were opened through CUDA IPC: every buffer carries its flag words
+    uint32_t peer_epoch = 0;
+    uint32_t* d_barrier_timeout = nullptr;
+    // Deferred render() / renderAgain() calls (rt_render, rt_render_again): consecutive samples with one camera are
+    // collected and rendered by ONE launch when something observes the image or the statistics (flush_pending) — the
+    // sqrt(mean) chain of those samples inside one launch is bit-identical to one launch per sample.
+    uint32_t pend_first = 0, pend_n = 0;
+    float pend_cam[12] = {0};
     bool count_work = false;          // rt_set_work_counting: LBVH renders go through the instrumented (untimed) kernel
     unsigned long long* d_work = nullptr;
     uint64_t work_counts[8] = {0};
@@ -485,6 +493,9 @@ int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
 // ================================================================================================ API
 extern "C" {
 
+static int flush_pending(rt_ctx* c);     // renders the recorded render() / renderAgain() calls (see rt_render)
+#define FLUSH(c) do { int fr_ = flush_pending(c); if (fr_ != RT_OK) return fr_; } while (0)
+
 const char* rt_last_error(void) { return g_last_error.c_str(); }
 int rt_set_error_message(int code, const char* msg) { return fail(code, "%s", msg ? msg : ""); }   // used by host/host_capi.cpp
 const char* rt_version(void) { return "rtb200 0.1 (sm_100a; strict+fast arithmetic; table+counter RNG)"; }
@@ -519,7 +530,11 @@ int rt_create(int width, int height, int device, rt_ctx** out) {
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaEventCreate(&c->ev2)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaMalloc(&c->d_image, px * sizeof(float4))) != cudaSuccess) return bail(e, "image buffer");
-    if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4))) != cudaSuccess) return bail(e, "accumulation buffer");
+    // the accumulation buffer carries the flag words of the device-side rank barrier behind its pixels (see PeerBarrier)
+    if ((e = cudaMalloc(&c->d_accum_own, px * sizeof(float4) + kPeerFlagWords * sizeof(uint32_t))) != cudaSuccess) return bail(e, "accumulation buffer");
+    cudaMemsetAsync(c->d_accum_own + px, 0, kPeerFlagWords * sizeof(uint32_t), c->stream);
+    if ((e = cudaMalloc(&c->d_barrier_timeout, sizeof(uint32_t))) != cudaSuccess) return bail(e, "barrier flag");
+    cudaMemsetAsync(c->d_barrier_timeout, 0, sizeof(uint32_t), c->stream);
     if ((e = cudaMalloc(&c->d_rays, 6 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "counters");   // rays, queries, -, queue, head segments, stochastic slots
     c->d_head_counts = c->d_rays + 4;
     c->d_accum = c->d_accum_own;
@@ -541,7 +556,7 @@ int rt_destroy(rt_ctx* c) {
         if (c->own_stream) cudaStreamSynchronize(c->own_stream);
         rt_close_peers(c);
         if (c->h_stage) cudaFreeHost(c->h_stage);
-        cudaFree(c->d_certify); cudaFree(c->d_work);
+        cudaFree(c->d_certify); cudaFree(c->d_work); cudaFree(c->d_barrier_timeout);
         cudaFree(c->d_head_rec); cudaFree(c->d_head_flag); cudaFree(c->d_head_list); cudaFree(c->d_head_key); cudaFree(c->d_head_key_sorted); cudaFree(c->d_head_iota); cudaFree(c->d_head_scratch); cudaFree(c->d_partial);
         cudaFree(c->d_block_cost); cudaFree(c->d_block_sorted); cudaFree(c->d_block_iota); cudaFree(c->d_block_order); cudaFree(c->d_block_scratch);
         cudaFree(c->d_image); cudaFree(c->d_accum_own); cudaFree(c->d_rays); cudaFree(c->d_table); cudaFree(c->d_tex);
@@ -559,12 +574,14 @@ int rt_destroy(rt_ctx* c) {
 
 int rt_set_stream(rt_ctx* c, void* s) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
+    FLUSH(c);
     c->stream = s ? (cudaStream_t)s : c->own_stream;
     return RT_OK;
 }
 
 int rt_upload_scene(rt_ctx* c, const rt_scene_desc* d) {
     if (!c || !d) return fail(RT_ERR_INVALID, "rt_upload_scene: null argument");
+    FLUSH(c);
     Guard g(c);
     c->have_scene = false;
     return convert_scene(c, d);
@@ -573,6 +590,7 @@ int rt_upload_scene(rt_ctx* c, const rt_scene_desc* d) {
 int rt_upload_textures(rt_ctx* c, const float* rgba, int w, int h, int layers) {
     if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_upload_textures: null argument");
     if (w <= 0 || h <= 0 || layers <= 0) return fail(RT_ERR_INVALID, "rt_upload_textures: bad size %d x %d x %d", w, h, layers);
+    FLUSH(c);
     Guard g(c);
     const size_t n = (size_t)w * h * layers;
     if (n != (size_t)c->tex.w * c->tex.h * c->tex.layers) {          // new size: allocate first, a failure keeps the old array
@@ -612,6 +630,7 @@ int rt_make_random_table(uint32_t seed, float* out) {
 int rt_set_random_table(rt_ctx* c, const float* table, uint32_t n_floats) {
     if (!c || !table) return fail(RT_ERR_INVALID, "rt_set_random_table: null argument");
     if (n_floats != RT_RANDOM_TABLE_FLOATS) return fail(RT_ERR_INVALID, "rt_set_random_table: expected %u floats", RT_RANDOM_TABLE_FLOATS);
+    FLUSH(c);
     Guard g(c);
     if (!c->d_table) CU(cudaMalloc(&c->d_table, (size_t)n_floats * sizeof(float)));
     CU(cudaMemcpyAsync(c->d_table, table, (size_t)n_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream));
@@ -623,11 +642,13 @@ int rt_set_params(rt_ctx* c, const rt_params* p) {
     if (!c || !p) return fail(RT_ERR_INVALID, "rt_set_params: null argument");
     if (p->max_depth == 0) return fail(RT_ERR_INVALID, "max_depth must be >= 1");
     if (p->rng_mode > 2 || p->arith > 1 || p->mesh_mode > 1 || p->accel > 2 || p->path_head > 1) return fail(RT_ERR_INVALID, "rt_set_params: enum out of range");
+    FLUSH(c);
     c->prm = *p;
     return RT_OK;
 }
 int rt_set_region(rt_ctx* c, int x0, int y0, int w, int h) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
+    FLUSH(c);
     if (w <= 0 || h <= 0) { c->rx0 = c->ry0 = 0; c->rx1 = c->W; c->ry1 = c->H; return RT_OK; }
     if (x0 < 0 || y0 < 0 || x0 > c->W - w || y0 > c->H - h)
         return fail(RT_ERR_INVALID, "rt_set_region: %d x %d at (%d, %d) does not lie inside the %d x %d frame", w, h, x0, y0, c->W, c->H);
@@ -724,13 +745,9 @@ static int order_blocks(rt_ctx* c, TraceLaunch& L, int* launches) {
     return RT_OK;
 }
 
+static int check_renderable(rt_ctx* c, const float* cam);
 static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, uint32_t accum_mode) {
-    if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
-    if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
-    if (c->prm.rng_mode != RT_RNG_COUNTER && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
-    if (c->max_texture_used >= (int64_t)c->tex.layers)
-        return fail(RT_ERR_STATE, "render: a textured mesh uses texture %lld but only %d layer(s) are uploaded",
-                    (long long)c->max_texture_used, c->tex.layers);
+    { int r = check_renderable(c, cam); if (r != RT_OK) return r; }
     if (n == 0) return RT_OK;
     Guard g(c);
     { int r = ensure_accel(c); if (r != RT_OK) return r; }
@@ -806,22 +823,59 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     return RT_OK;
 }
 
+// The reference finishes its queue after every sample (src/raytracer.cpp:140,161), one launch + one host round trip per
+// sample (184 us per 1080p sample through this API in round 1 against 70 us of kernel work).  Nothing can see the image
+// between two renderAgain() calls unless it is read, so rt_render / rt_render_again only validate and record the call; the
+// recorded samples are rendered by one launch of the batched kernel when the image, the statistics or any state they
+// depend on is touched.  Bit-identical to eager execution (tests/test_gpu_parity.py::test_strict_image_bit_exact).
+static const uint32_t kMaxPending = 4096;
+static int flush_pending(rt_ctx* c) {
+    if (!c || c->pend_n == 0) return RT_OK;
+    const uint32_t first = c->pend_first, n = c->pend_n;
+    c->pend_n = 0;
+    return do_render(c, c->pend_cam, first, n, RT_ACCUM_REFERENCE);
+}
+static int check_renderable(rt_ctx* c, const float* cam) {
+    if (!c || !cam) return fail(RT_ERR_INVALID, "render: null argument");
+    if (!c->have_scene) return fail(RT_ERR_STATE, "render: no scene uploaded");
+    if (c->prm.rng_mode != RT_RNG_COUNTER && !c->d_table) return fail(RT_ERR_STATE, "render: table RNG selected but no random table set");
+    if (c->max_texture_used >= (int64_t)c->tex.layers)
+        return fail(RT_ERR_STATE, "render: a textured mesh uses texture %lld but only %d layer(s) are uploaded",
+                    (long long)c->max_texture_used, c->tex.layers);
+    return RT_OK;
+}
 int rt_render(rt_ctx* c, const float cam[12]) {
-    if (!c) return fail(RT_ERR_INVALID, "null context");
+    { int r = check_renderable(c, cam); if (r != RT_OK) return r; }
+    c->pend_n = 0;                                   // recorded samples of the previous image would be overwritten unseen
     c->stats.rays_total = 0;
-    int r = do_render(c, cam, 0u, 1u, RT_ACCUM_REFERENCE);
-    if (r == RT_OK) { c->sample_counter = 0; c->stats.samples_done = 1; }
-    return r;
+    if (std::getenv("RTB200_EAGER")) {
+        int r = do_render(c, cam, 0u, 1u, RT_ACCUM_REFERENCE);
+        if (r == RT_OK) { c->sample_counter = 0; c->stats.samples_done = 1; }
+        return r;
+    }
+    std::memcpy(c->pend_cam, cam, 48);
+    c->pend_first = 0; c->pend_n = 1;
+    c->sample_counter = 0; c->stats.samples_done = 1;
+    return RT_OK;
 }
 int rt_render_again(rt_ctx* c, const float cam[12]) {
-    if (!c) return fail(RT_ERR_INVALID, "null context");
-    int r = do_render(c, cam, c->sample_counter + 1u, 1u, RT_ACCUM_REFERENCE);
-    if (r == RT_OK) { c->sample_counter += 1; c->stats.samples_done = c->sample_counter + 1; }
-    return r;
+    { int r = check_renderable(c, cam); if (r != RT_OK) return r; }
+    if (std::getenv("RTB200_EAGER")) {
+        FLUSH(c);
+        int r = do_render(c, cam, c->sample_counter + 1u, 1u, RT_ACCUM_REFERENCE);
+        if (r == RT_OK) { c->sample_counter += 1; c->stats.samples_done = c->sample_counter + 1; }
+        return r;
+    }
+    if (c->pend_n && (std::memcmp(c->pend_cam, cam, 48) != 0 || c->pend_n >= kMaxPending)) FLUSH(c);
+    if (c->pend_n == 0) { std::memcpy(c->pend_cam, cam, 48); c->pend_first = c->sample_counter + 1u; }
+    c->pend_n += 1;
+    c->sample_counter += 1; c->stats.samples_done = c->sample_counter + 1;
+    return RT_OK;
 }
 int rt_render_samples(rt_ctx* c, const float cam[12], uint32_t first, uint32_t n, uint32_t accum_mode) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (accum_mode > 1) return fail(RT_ERR_INVALID, "bad accum_mode");
+    FLUSH(c);
     if (accum_mode == RT_ACCUM_REFERENCE && first == 0) c->stats.rays_total = 0;
     int r = do_render(c, cam, first, n, accum_mode);
     if (r == RT_OK && n) {
@@ -832,6 +886,7 @@ int rt_render_samples(rt_ctx* c, const float cam[12], uint32_t first, uint32_t n
 }
 int rt_clear_accum(rt_ctx* c) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
+    FLUSH(c);
     Guard g(c);
     CU(cudaMemsetAsync(c->d_accum, 0, (size_t)c->W * c->H * sizeof(float4), c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -840,6 +895,7 @@ int rt_clear_accum(rt_ctx* c) {
 }
 int rt_invalidate_caches(rt_ctx* c) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
+    FLUSH(c);
     c->head_valid = false;
     c->certify_valid = false;
     return RT_OK;
@@ -847,6 +903,7 @@ int rt_invalidate_caches(rt_ctx* c) {
 int rt_finalize(rt_ctx* c, uint32_t spp) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize: spp must be > 0");
+    FLUSH(c);
     Guard g(c);
     CU(launch_finalize(c->d_accum, c->d_image, c->W * c->H, spp, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -856,6 +913,7 @@ int rt_finalize(rt_ctx* c, uint32_t spp) {
 
 int rt_read_image(rt_ctx* c, float* rgba) {
     if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_read_image: null argument");
+    FLUSH(c);
     Guard g(c);
     CU(cudaMemcpyAsync(rgba, c->d_image, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -863,6 +921,7 @@ int rt_read_image(rt_ctx* c, float* rgba) {
 }
 int rt_read_accum(rt_ctx* c, float* rgba) {
     if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_read_accum: null argument");
+    FLUSH(c);
     Guard g(c);
     CU(cudaMemcpyAsync(rgba, c->d_accum, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -871,6 +930,7 @@ int rt_read_accum(rt_ctx* c, float* rgba) {
 int rt_restore_image(rt_ctx* c, const float* rgba, uint32_t samples) {
     if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_restore_image: null argument");
     if (samples == 0) return fail(RT_ERR_INVALID, "rt_restore_image: an image holds at least one sample");
+    FLUSH(c);
     Guard g(c);
     CU(cudaMemcpyAsync(c->d_image, rgba, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -880,6 +940,7 @@ int rt_restore_image(rt_ctx* c, const float* rgba, uint32_t samples) {
 }
 int rt_restore_accum(rt_ctx* c, const float* rgba, uint32_t samples) {
     if (!c || !rgba) return fail(RT_ERR_INVALID, "rt_restore_accum: null argument");
+    FLUSH(c);
     Guard g(c);
     CU(cudaMemcpyAsync(c->d_accum, rgba, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -888,6 +949,7 @@ int rt_restore_accum(rt_ctx* c, const float* rgba, uint32_t samples) {
 }
 int rt_get_stats(rt_ctx* c, rt_stats* s) {
     if (!c || !s) return fail(RT_ERR_INVALID, "rt_get_stats: null argument");
+    FLUSH(c);
     *s = c->stats;
     return RT_OK;
 }
@@ -899,6 +961,7 @@ int rt_accum_device_ptr(rt_ctx* c, void** p, size_t* bytes) {
 }
 int rt_image_device_ptr(rt_ctx* c, void** p, size_t* bytes) {
     if (!c || !p) return fail(RT_ERR_INVALID, "null argument");
+    FLUSH(c);
     *p = c->d_image;
     if (bytes) *bytes = (size_t)c->W * c->H * sizeof(float4);
     return RT_OK;
@@ -922,11 +985,12 @@ int rt_close_peers(rt_ctx* c) {
     }
     if (c->peer_image_opened && c->peer_image0) cudaIpcCloseMemHandle(c->peer_image0);
     c->peer_image0 = nullptr; c->peer_image_opened = false;
-    c->peer_n = 0;
+    c->peer_n = 0; c->peer_flags_ok = false;
     return RT_OK;
 }
 int rt_ipc_export(rt_ctx* c, void* accum_handle, void* image_handle) {
     if (!c || !accum_handle || !image_handle) return fail(RT_ERR_INVALID, "rt_ipc_export: null argument");
+    FLUSH(c);
     static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "CUDA IPC handle size");
     if (c->d_accum != c->d_accum_own) return fail(RT_ERR_STATE, "rt_ipc_export: the context accumulates into a caller buffer; only the context's own buffer can be exported");
     Guard g(c);
@@ -957,6 +1021,7 @@ int rt_ipc_open_peers(rt_ctx* c, int n, int rank, const void* accum_handles, con
         c->peer_image_opened = true;
     }
     c->peer_n = n; c->peer_rank = rank;
+    c->peer_flags_ok = true;                      // peer_epoch keeps counting: the flag words only ever grow
     return RT_OK;
 }
 int rt_set_peers_direct(rt_ctx* c, int n, int rank, void* const* accum_ptrs, void* image0) {
@@ -971,12 +1036,25 @@ int rt_set_peers_direct(rt_ctx* c, int n, int rank, void* const* accum_ptrs, voi
     c->peer_n = n; c->peer_rank = rank;
     return RT_OK;
 }
-static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync);
-int rt_finalize_peers(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, true); }
-int rt_finalize_peers_async(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, false); }
-static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync) {
+static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync, bool barriers);
+int rt_finalize_peers(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, true, false); }
+int rt_finalize_peers_async(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, false, false); }
+int rt_finalize_peers_barrier_async(rt_ctx* c, uint32_t spp) { return finalize_peers(c, spp, false, true); }
+static int peer_barrier(rt_ctx* c, int phase) {
+    PeerBarrier B{};
+    const size_t px = (size_t)c->W * c->H;
+    for (int r = 0; r < c->peer_n; ++r) B.flags[r] = reinterpret_cast<uint32_t*>((float4*)c->peer_accum[r] + px);
+    B.n_ranks = c->peer_n; B.my_rank = c->peer_rank; B.phase = phase; B.epoch = c->peer_epoch;
+    B.timeout_cycles = 20000000000ll;                          // ~10 s: a dead rank turns into an error, not a hung device
+    B.timed_out = c->d_barrier_timeout;
+    CU(launch_peer_barrier(B, c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync, bool barriers) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize_peers: spp must be > 0");
+    FLUSH(c);
     if (c->peer_n < 1) return fail(RT_ERR_STATE, "rt_finalize_peers: no peers set (rt_ipc_open_peers / rt_set_peers_direct)");
     Guard g(c);
     PeerFinalize P{};
@@ -987,9 +1065,24 @@ static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync) {
     P.first_pixel = (int)(px * c->peer_rank / c->peer_n);
     P.n_pixels = (int)(px * (c->peer_rank + 1) / c->peer_n) - P.first_pixel;
     P.inv_spp = 1.0f / (float)spp;
+    if (barriers) {
+        if (!c->peer_flags_ok) return fail(RT_ERR_STATE, "rt_finalize_peers_barrier_async: the device-side barrier needs peers opened with rt_ipc_open_peers");
+        c->peer_epoch += 1;
+        { int r = peer_barrier(c, 0); if (r != RT_OK) return r; }          // every rank's render is complete
+    }
     CU(launch_finalize_peers(P, c->stream));
+    if (barriers) { int r = peer_barrier(c, 1); if (r != RT_OK) return r; }  // every slice of rank 0's image is written
     if (sync) CU(cudaStreamSynchronize(c->stream));
     c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+int rt_peer_barrier_status(rt_ctx* c, int* timed_out) {
+    if (!c || !timed_out) return fail(RT_ERR_INVALID, "rt_peer_barrier_status: null argument");
+    Guard g(c);
+    uint32_t v = 0;
+    CU(cudaMemcpyAsync(&v, c->d_barrier_timeout, sizeof v, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *timed_out = (int)v;
     return RT_OK;
 }
 

@@ -185,6 +185,18 @@ struct PeerFinalize {          // k_finalize_peers: sum of n_ranks accumulation 
     float inv_spp;
 };
 cudaError_t launch_finalize_peers(const PeerFinalize& p, cudaStream_t s);
+// Barrier of the ranks of the sample split on the device: arrival flags in peer memory instead of two NCCL collectives
+// around k_finalize_peers.  Every rank owns kPeerFlagWords words behind its accumulation buffer (visible to the peers through
+// the same CUDA IPC mapping); phase 0 = "my render is complete", phase 1 = "my slice of the image is written".
+constexpr int kPeerFlagWords = 2 * kMaxPeers;
+struct PeerBarrier {
+    uint32_t* flags[kMaxPeers];   // flags[r] = rank r's flag words (peer pointers; [my_rank] is local)
+    int n_ranks, my_rank, phase;
+    uint32_t epoch;               // grows by one per barrier round; flags only ever grow
+    long long timeout_cycles;     // a rank that never arrives must not hang the device
+    uint32_t* timed_out;          // local device word, set when the wait gave up
+};
+cudaError_t launch_peer_barrier(const PeerBarrier& b, cudaStream_t s);
 cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t s);
 
 }  // namespace rtb

@@ -220,18 +220,32 @@ __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 
         }
     }
 }
-// The reference's sphere test computes dis = b*b - (oc.oc - r*r) in binary32 (cl:152-155): its absolute error grows
-// like ~12 eps |oc|^2, so from a distance D it reports hits up to sqrt(r^2 + 7e-7 D^2) - r OUTSIDE the sphere
-// (8.5e-4 D for a small sphere).  Brute force returns those hits, so a traversal that must return the same nearest hit
-// has to visit every box the ray passes within that distance: the box is inflated by kSlabSlack x (an upper bound of
-// the distance from the ray origin to its farthest corner) before the slab test.  Twelve more instructions per box;
-// RT_BVH_FAST_SLAB (fast-arithmetic render kernel only) drops the inflation.
+// The reference's sphere test computes dis = b*b - (oc.oc - r*r) in binary32 (cl:152-155) and ASSUMES a unit direction.
+// Two consequences a traversal that must return brute force's nearest hit has to live with:
+//  (1) rounding: the absolute error of dis grows like ~12 eps |oc|^2, so from a distance D the test reports hits up to
+//      sqrt(r^2 + 7e-7 D^2) - r OUTSIDE the sphere (8.5e-4 D for a small sphere);
+//  (2) refracted directions are not normalised (cl:386,428) and sphere normals are (p - c) / r of an inexact hit point
+//      (cl:160), so |d|^2 = a drifts away from 1 along glass chains (C5: 8 % of the queries have a - 1 > 1e-3, the
+//      largest is 6).  With b = oc.d the test accepts dis > 0  <=>  p^2 < r^2 + (a - 1) b_u^2  (p = distance of the centre
+//      from the ray, b_u = its distance along the ray): for a > 1 the sphere "flares" with distance and brute force
+//      reports hits on spheres the ray passes at up to sqrt(a - 1) b_u (found by tests/test_gpu_crops.py: 6 % of the
+//      pixels of the C5 crop differed before this was handled; the default scene's few big spheres never showed it).
+// So every box that can hold a sphere or lens is inflated, before the slab test, by slack x (an upper bound of the
+// distance from the ray origin to its farthest corner), slack = ray_slack(d) >= sqrt(7e-7 max(1, a) + max(a - 1, 0)), 1e-3 for a unit direction.
+// Twelve more instructions per box; triangle-only nodes (BvhNode::flags == 0) do not need it in the fast arm — Moller-
+// Trumbore is exact in any parametrisation.
 #define RT_SLAB_SLACK 1.0e-3f
+__device__ __forceinline__ float ray_slack(V3 d) {
+    // shell^2 <= 7e-7 max(1, a) D^2 (rounding of dis) + max(a - 1, 0) b_u^2 (flare), b_u <= D; 2 % margin.  A normalised
+    // direction (|a - 1| <= 2.4e-7) gets exactly the round-1 slack of 1e-3.
+    const float a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
+    return fmaxf(RT_SLAB_SLACK, 1.02f * sqrtf(fmaf(7e-7f, fmaxf(1.0f, a), fmaxf(a - 1.0f, 0.0f))));
+}
 template <bool ROBUST>
-__device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near) {
+__device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK) {
     float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
     if (ROBUST) {
-        const float dl = RT_SLAB_SLACK * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
+        const float dl = slack * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
         l0 -= dl; h0 += dl; l1 -= dl; h1 += dl; l2 -= dl; h2 += dl;
     }
     const float ax = l0 * inv.x, bx = h0 * inv.x;
@@ -241,16 +255,12 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
     return t_near <= t_far && t_near <= t_best;
 }
-#ifdef RT_BVH_FAST_SLAB
-#define RT_RENDER_SLAB slab<A::kExact>
-#else
-#define RT_RENDER_SLAB slab<true>
-#endif
 template <class A>
 __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
     if (bvh.n_leaves == 0u) return;
     if (bvh.root < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~bvh.root), o, d, best); return; }
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const float slack = ray_slack(d);
     int stack[kBvhStack];
     int sp = 0, node = bvh.root;
     for (;;) {
@@ -259,7 +269,7 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
         const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
-        bool h0 = slab<true>(lo0, hi0, o, inv, best.t, t0), h1 = slab<true>(lo1, hi1, o, inv, best.t, t1);
+        bool h0 = slab<true>(lo0, hi0, o, inv, best.t, t0, slack), h1 = slab<true>(lo1, hi1, o, inv, best.t, t1, slack);
         if (h0 && c0 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c0), o, d, best); h0 = false; }
         if (h1 && c1 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c1), o, d, best); h1 = false; }
         if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
@@ -743,6 +753,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
 
     Hit h;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
+    float slack = RT_SLAB_SLACK;
     int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false;
@@ -752,6 +763,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
         if (traversing && node < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~node), o, d, h); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+        slack = ray_slack(d);
     };
     bool has_ray = k < k_end;
     if (has_ray) start_ray();
@@ -764,7 +776,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
-                bool h0 = RT_RENDER_SLAB(lo0, hi0, o, inv, h.t, t0), h1 = RT_RENDER_SLAB(lo1, hi1, o, inv, h.t, t1);
+                bool h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, slack), h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, slack);
                 if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
                 if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
                 if (h0 && h1) {
@@ -1022,10 +1034,10 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 //     keeps the inflated test everywhere (its equality with brute force is what tests/test_gpu_bvh.py pins).
 //   * Leaves: a trip tests at most two leaves per lane through ONE copy of the leaf code (lanes whose first or second
 //     child is a leaf run it together).
-//   * Traversal stack: the first RT_BVH_SSTACK levels in shared memory ([level][thread], conflict free), the rest —
-//     practically never used — in local memory.
+//   * Traversal stack: in local memory (L1).  RT_BVH_SSTACK > 0 keeps the first levels in shared memory ([level][thread],
+//     conflict free) — measured 4 % SLOWER on C4 and C5 (r02a probes: 5.25 vs 5.49 / 3.39 vs 3.60 Grays/s), so it is off.
 #ifndef RT_BVH_SSTACK
-#define RT_BVH_SSTACK 24
+#define RT_BVH_SSTACK 0
 #endif
 #ifndef RT_BVH_FLAG_SLAB
 #define RT_BVH_FLAG_SLAB 1
@@ -1067,6 +1079,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
+    float slack = RT_SLAB_SLACK;
     int sp = 0, node = 0;
     bool traversing = false, has_ray = false, have_result = false, exhausted = false;
     auto push = [&](int v) {
@@ -1082,6 +1095,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
         if (traversing && node < 0) { bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~node), o, d, h, &wc); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+        slack = ray_slack(d);
         have_result = true;
     };
 
@@ -1147,7 +1161,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 if (RT_BVH_FLAG_SLAB && !A::kExact && __float_as_uint(n2.w) == 0u) {
                     h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
                 } else {
-                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1);
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, slack); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, slack);
                 }
                 int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
                 if (l0 == 0) { l0 = l1; l1 = 0; }

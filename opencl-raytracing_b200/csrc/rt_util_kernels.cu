@@ -39,6 +39,27 @@ cudaError_t launch_finalize_peers(const PeerFinalize& p, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// One warp: lane r releases this rank's arrival word in rank r's memory (everything this rank's stream wrote before is
+// made visible first), then spins on the word rank r released here.  Flags are monotonic epochs, so nothing is ever reset.
+__global__ void __launch_bounds__(32) k_peer_barrier(const __grid_constant__ PeerBarrier b) {
+    const int r = (int)threadIdx.x;
+    if (r >= b.n_ranks) return;
+    const int word = b.phase * kMaxPeers;
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t*>(b.flags[r] + word + b.my_rank) = b.epoch;
+    const volatile uint32_t* mine = reinterpret_cast<volatile uint32_t*>(b.flags[b.my_rank] + word + r);
+    const long long t0 = clock64();
+    while ((int32_t)(*mine - b.epoch) < 0) {
+        if (clock64() - t0 > b.timeout_cycles) { *b.timed_out = 1u; break; }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+cudaError_t launch_peer_barrier(const PeerBarrier& b, cudaStream_t s) {
+    k_peer_barrier<<<1, 32, 0, s>>>(b);
+    return cudaGetLastError();
+}
+
 // Sample chunks of k_trace_tail_* (TraceLaunch::chunks): the sums of a pixel's chunks, added to its accumulator in
 // chunk order (deterministic; 16 B per lane, the chunk planes are read coalesced).
 __global__ void __launch_bounds__(256) k_combine_chunks(const float4* __restrict__ partial, const uint32_t* __restrict__ list,

@@ -90,7 +90,7 @@ int rt_write_tga(const char* path, const float* rgba, int w, int h) {
             const float* p = rgba + 4 * ((size_t)y * w + x);
             for (int c = 0; c < 3; ++c) {
                 float v = p[2 - c];                    // BGR
-                v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+                v = !(v >= 0.0f) ? 0.0f : (v > 1.0f ? 1.0f : v);   // NaN -> 0 (a float -> unsigned char cast of NaN is undefined)
                 row[3 * x + c] = (unsigned char)(v * 255.0f + 0.5f);
             }
         }

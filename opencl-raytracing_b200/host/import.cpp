@@ -140,21 +140,30 @@ bool load_png(const std::string& path, Image8& out, std::string* why) {
     uint32_t w = 0, h = 0;
     int depth = 0, ctype = 0, interlace = 0;
     std::vector<uint8_t> idat;
+    bool first_chunk = true;
     while (p + 12 <= buf.size()) {
         const uint32_t len = be32(&buf[p]);
         const char* type = (const char*)&buf[p + 4];
-        if (p + 12 + len > buf.size()) return fail("truncated chunk");
+        if ((uint64_t)p + 12u + len > buf.size()) return fail("truncated chunk");
         const uint8_t* d = &buf[p + 8];
-        if (!std::memcmp(type, "IHDR", 4)) { w = be32(d); h = be32(d + 4); depth = d[8]; ctype = d[9]; interlace = d[12]; }
+        if (first_chunk != !std::memcmp(type, "IHDR", 4)) return fail("IHDR must be the first chunk, once");
+        first_chunk = false;
+        if (!std::memcmp(type, "IHDR", 4)) {
+            if (len != 13) return fail("bad IHDR length");
+            w = be32(d); h = be32(d + 4); depth = d[8]; ctype = d[9]; interlace = d[12];
+        }
         else if (!std::memcmp(type, "IDAT", 4)) idat.insert(idat.end(), d, d + len);
         else if (!std::memcmp(type, "IEND", 4)) break;
         p += 12 + len;
     }
     if (!w || !h) return fail("missing IHDR");
+    if ((uint64_t)w * h > (1ull << 28)) return fail("image larger than 2^28 pixels");
     if (depth != 8 || interlace != 0) return fail("only 8-bit non-interlaced PNG is supported");
     int ch;
     switch (ctype) { case 0: ch = 1; break; case 2: ch = 3; break; case 4: ch = 2; break; case 6: ch = 4; break; default: return fail("palette PNG is not supported"); }
     const size_t stride = (size_t)w * ch;
+    // deflate expands at most ~1032 : 1: a data stream too short for the declared size is refused before allocating
+    if ((uint64_t)idat.size() * 1100u + 64u < (uint64_t)(stride + 1) * h) return fail("zlib inflate failed");
     std::vector<uint8_t> raw((stride + 1) * h);
     uLongf raw_len = raw.size();
     if (uncompress(raw.data(), &raw_len, idat.data(), idat.size()) != Z_OK || raw_len != raw.size()) return fail("zlib inflate failed");

@@ -7,8 +7,12 @@
 //               [--arith strict|fast] [--rng table|counter] [--table-seed S] [--fov DEG] [--pos x,y,z]
 //               [--yaw DEG] [--pitch DEG] [--script FILE] [--out img.tga] [--raw img.f32]
 //               [--checkpoint FILE] [--resume FILE]
-//   checkpoint file: "RTCK" u32 width, height, samples, then width*height*4 float32 of the (sqrt(mean),1) image; --resume
-//   restores it (rt_restore_image) and continues with renderAgain, bit-identical to an uninterrupted run
+//   checkpoint file: "RTC2" u32 width, height, samples, u64 fingerprint, then width*height*4 float32 of the (sqrt(mean),1)
+//   image; --resume restores it (rt_restore_image) and continues with renderAgain, bit-identical to an uninterrupted run.
+//   The fingerprint (FNV-1a) covers everything the continuation depends on — the 12 camera floats, max depth, arithmetic and
+//   RNG mode, the scene file name and RT_TABLE_SEED — and a resume with a different fingerprint is refused.  The random table
+//   is seeded from std::random_device unless RT_TABLE_SEED pins it (src/raytracer.cpp:73-74 does the same): without a pinned
+//   seed a checkpoint cannot be continued bit-identically and --checkpoint / --resume say so.
 //   script lines:  move forward|back|left|right DT | rotate DX DY | zoom SCROLL | fast 0|1 | slow 0|1 | frames N
 #include <chrono>
 #include <cstdio>
@@ -51,15 +55,32 @@ int main(int argc, char** argv) {
     }
     Camera camera(fov, (float)W / (float)H, glm::vec3(pos[0], pos[1], pos[2]), yaw, pitch);
     RayTracer tracer(W, H, "kernels/raytracer.cl");
+    auto fingerprint = [&]() {
+        uint64_t hsh = 1469598103934665603ull;
+        auto mix = [&](const void* p, size_t n) { for (size_t k = 0; k < n; ++k) { hsh ^= ((const unsigned char*)p)[k]; hsh *= 1099511628211ull; } };
+        mix(camera.transferData(), 48);
+        rt_params prm;
+        rt_get_params(tracer.context(), &prm);
+        mix(&prm.max_depth, 4); mix(&prm.arith, 4); mix(&prm.rng_mode, 4); mix(&prm.mesh_mode, 4);
+        for (const char* name : {"RT_SCENE_FILE", "RT_TABLE_SEED"}) { const char* v = std::getenv(name); if (v) mix(v, std::strlen(v)); mix("|", 1); }
+        return hsh;
+    };
+    if ((!ckpt_in.empty() || !ckpt_out.empty()) && !std::getenv("RT_TABLE_SEED"))
+        std::fprintf(stderr, "warning: no --table-seed: the random table of this run cannot be reproduced, a resumed run will not be bit-identical\n");
 
     bool camera_in_motion = true;                       // main.cpp:48: the first frame is a render()
     if (!ckpt_in.empty()) {
         std::ifstream f(ckpt_in, std::ios::binary);
         char magic[4] = {0};
         uint32_t hdr[3] = {0, 0, 0};
-        f.read(magic, 4); f.read((char*)hdr, sizeof hdr);
-        if (!f || std::memcmp(magic, "RTCK", 4) != 0 || hdr[0] != (uint32_t)W || hdr[1] != (uint32_t)H || hdr[2] == 0) {
+        uint64_t fp = 0;
+        f.read(magic, 4); f.read((char*)hdr, sizeof hdr); f.read((char*)&fp, sizeof fp);
+        if (!f || std::memcmp(magic, "RTC2", 4) != 0 || hdr[0] != (uint32_t)W || hdr[1] != (uint32_t)H || hdr[2] == 0) {
             std::fprintf(stderr, "cannot resume from %s (missing, damaged, or a different frame size)\n", ckpt_in.c_str());
+            return 2;
+        }
+        if (fp != fingerprint()) {
+            std::fprintf(stderr, "cannot resume from %s: it was written with a different camera, depth, arithmetic / RNG mode, scene or table seed\n", ckpt_in.c_str());
             return 2;
         }
         std::vector<float> img((size_t)W * H * 4);
@@ -105,7 +126,8 @@ int main(int argc, char** argv) {
     if (!ckpt_out.empty()) {
         std::ofstream o(ckpt_out, std::ios::binary);
         const uint32_t hdr[3] = {(uint32_t)W, (uint32_t)H, st.samples_done};
-        o.write("RTCK", 4); o.write((const char*)hdr, sizeof hdr); o.write((const char*)img.data(), (std::streamsize)(img.size() * 4));
+        const uint64_t fp = fingerprint();
+        o.write("RTC2", 4); o.write((const char*)hdr, sizeof hdr); o.write((const char*)&fp, sizeof fp); o.write((const char*)img.data(), (std::streamsize)(img.size() * 4));
     }
     if (!out_raw.empty()) { std::ofstream o(out_raw, std::ios::binary); o.write((const char*)img.data(), (std::streamsize)(img.size() * 4)); }
     std::printf("{\"frames\": %ld, \"samples_in_image\": %u, \"width\": %d, \"height\": %d, \"rays\": %llu, \"seconds\": %.4f, \"mrays_per_s\": %.1f}\n",

@@ -201,7 +201,10 @@ void SceneCreator::loadTextures() {
     for (size_t id = 0; id < texture_paths.size(); ++id) {
         rthost::Image8 im;
         std::string why;
-        if (!rthost::load_png(resolveTexture(texture_paths[id]), im, &why)) scene_error("ERROR: STBimage: COULD NOT FIND THE TEXTURE");
+        bool ok = false;
+        try { ok = rthost::load_png(resolveTexture(texture_paths[id]), im, &why); }
+        catch (const std::exception&) { ok = false; }                      // e.g. bad_alloc on a damaged header: the reference's error path, not terminate()
+        if (!ok) scene_error("ERROR: STBimage: COULD NOT FIND THE TEXTURE");
         if (id == 0) { tex_width = im.width; tex_height = im.height; }
         else if (im.width != tex_width || im.height != tex_height)
             scene_error("ERROR: TEXTURES HAVE DIFFERENT SIZES: TEMPLATE: " + std::to_string(tex_width) + " x " + std::to_string(tex_height) +

@@ -76,7 +76,7 @@ def lib():
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
         "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
         "rt_ipc_export": [vp, vp, vp], "rt_ipc_open_peers": [vp, ci, ci, vp, vp],
-        "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_finalize_peers_async": [vp, u32], "rt_close_peers": [vp],
+        "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_finalize_peers_async": [vp, u32], "rt_finalize_peers_barrier_async": [vp, u32], "rt_peer_barrier_status": [vp, C.POINTER(ci)], "rt_close_peers": [vp],
         "rt_measure_fp32_peak": [ci, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rt_scene_load": [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)], "rt_scene_get_desc": [vp, C.POINTER(SceneDesc)],
         "rt_scene_get_textures": [vp, C.POINTER(vp), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)],
@@ -325,6 +325,15 @@ class Context:
 
     def finalize_peers(self, spp, sync=True):
         _check((self.L.rt_finalize_peers if sync else self.L.rt_finalize_peers_async)(self.h, spp))
+
+    def finalize_peers_barrier(self, spp):
+        """Fused reduce + finalize bracketed by the device-side rank barrier; enqueue only."""
+        _check(self.L.rt_finalize_peers_barrier_async(self.h, spp))
+
+    def peer_barrier_timed_out(self):
+        v = C.c_int(0)
+        _check(self.L.rt_peer_barrier_status(self.h, C.byref(v)))
+        return bool(v.value)
 
     def close_peers(self):
         _check(self.L.rt_close_peers(self.h))

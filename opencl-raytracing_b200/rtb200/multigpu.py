@@ -33,11 +33,13 @@ class PeerFinalize:
     """Fused reduce + finalize over peer memory.  Handles are exchanged once (all_gather_object); per render every
     rank calls finalize(spp) between two barriers."""
 
-    def __init__(self, ctx, group=None, stream_ordered=False):
+    def __init__(self, ctx, group=None, stream_ordered=False, device_barrier=False):
         """stream_ordered: the context renders on torch's current CUDA stream (rt_set_stream); the two rank barriers
-        are then tiny all-reduces ordered on that stream and nothing blocks the host until the caller synchronises."""
+        are then tiny all-reduces ordered on that stream and nothing blocks the host until the caller synchronises.
+        device_barrier: no collective at all — the ranks meet through arrival words in peer memory
+        (rt_finalize_peers_barrier_async); everything stays on the context's stream."""
         import torch.distributed as dist
-        self.ctx, self.group, self.stream_ordered = ctx, group, stream_ordered
+        self.ctx, self.group, self.stream_ordered, self.device_barrier = ctx, group, stream_ordered, device_barrier
         self.flag = None
         if stream_ordered:
             import torch
@@ -50,6 +52,9 @@ class PeerFinalize:
 
     def finalize(self, spp):
         import torch.distributed as dist
+        if self.device_barrier:
+            self.ctx.finalize_peers_barrier(spp)
+            return
         if self.stream_ordered:
             dist.all_reduce(self.flag, group=self.group)      # every rank's render kernel is behind this on its stream
             self.ctx.finalize_peers(spp, sync=False)

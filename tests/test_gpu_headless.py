@@ -71,7 +71,7 @@ def test_headless_checkpoint_resume_is_bit_identical(tmp_path):
     for d in (a_dir, b_dir, c_dir):
         d.mkdir()
     info_a, _ = run(common + ["--spp", "3", "--checkpoint", ck], a_dir)
-    assert info_a["samples_in_image"] == 3 and os.path.getsize(ck) == 16 + W * H * 16
+    assert info_a["samples_in_image"] == 3 and os.path.getsize(ck) == 24 + W * H * 16      # "RTC2", w, h, samples, u64 fingerprint
     info_b, raw_b = run(common + ["--spp", "4", "--resume", ck], b_dir)
     info_c, raw_c = run(common + ["--spp", "7"], c_dir)
     assert info_b["samples_in_image"] == 7 and info_c["samples_in_image"] == 7
@@ -79,3 +79,13 @@ def test_headless_checkpoint_resume_is_bit_identical(tmp_path):
     bad = subprocess.run([EXE, "--scene", "shapes.scene", "--root", ASSETS, "--textures", ASSETS, "--width", "64", "--height", "64",
                           "--resume", ck], capture_output=True, text=True, timeout=120)
     assert bad.returncode == 2 and "cannot resume" in bad.stderr
+    # a checkpoint continued with another camera, depth, arithmetic / RNG mode or table seed is refused, not blended
+    for change in (["--depth", "11"], ["--table-seed", "10"], ["--yaw", "3"], ["--arith", "fast"]):
+        args = list(common)
+        if change[0] in args:
+            args[args.index(change[0]) + 1] = change[1]
+        else:
+            args += change
+        r = subprocess.run([EXE, "--scene", "shapes.scene", "--root", ASSETS, "--textures", ASSETS] + args + ["--spp", "1", "--resume", ck],
+                           capture_output=True, text=True, timeout=120)
+        assert r.returncode == 2 and "different camera, depth" in r.stderr, (change, r.stderr)

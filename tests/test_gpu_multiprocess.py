@@ -1,7 +1,8 @@
 """The REAL multi-process path of the sample split: one process per GPU (torchrun, NCCL), CUDA IPC handles exchanged with
 rt_ipc_export / rt_ipc_open_peers, every rank renders its global sample range, rt_finalize_peers_async sums the ranks'
 buffers over NVLink peer loads into rank 0's image.  The N-rank picture must equal the picture rank 0 renders alone to
-float-summation tolerance (2e-6 on the sqrt(mean) image) — for the fused exchange and for the NCCL reduce.
+float-summation tolerance (2e-6 on the sqrt(mean) image) — for the fused exchange (between host barriers, between NCCL
+barriers on the stream, and with the device-side arrival-flag barrier) and for the NCCL reduce.
 Skipped on boxes with one GPU (bench.py runs the same check at every N > 1 and prints it as "multi_gpu_check")."""
 import json
 import os
@@ -30,7 +31,7 @@ def _main(out_path):
     table = rtb200.make_random_table(12345)
     results = {}
     for arith in ("strict", "fast"):
-        for mode in ("fused", "fused_stream", "nccl"):
+        for mode in ("fused", "fused_stream", "fused_flags", "nccl"):
             ctx = rtb200.Context(W, H, local)
             ctx.set_params(max_depth=30, rng_mode=rtb200.RNG_COUNTER_TABLE, seed=1,
                            arith=rtb200.ARITH_STRICT if arith == "strict" else rtb200.ARITH_FAST)
@@ -46,11 +47,19 @@ def _main(out_path):
                     if rank == 0:
                         ctx.finalize(spp)
             else:
-                if mode == "fused_stream":
+                if mode != "fused":
                     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-                peers = PeerFinalize(ctx, stream_ordered=(mode == "fused_stream"))
+                peers = PeerFinalize(ctx, stream_ordered=(mode == "fused_stream"), device_barrier=(mode == "fused_flags"))
                 fin = peers.finalize
             r = split_image_check(ctx, cam, 24, world, rank, fin)
+            if mode == "fused_flags":
+                for _ in range(3):                      # the epochs keep counting: repeated rounds on the same contexts
+                    r2 = split_image_check(ctx, cam, 24, world, rank, fin)
+                    if rank == 0:
+                        r["ok"] = r["ok"] and r2["ok"]
+                timed_out = ctx.peer_barrier_timed_out()
+                if rank == 0:
+                    r["ok"] = r["ok"] and not timed_out
             if rank == 0:
                 results["%s/%s" % (arith, mode)] = r
             if mode != "nccl":
@@ -75,7 +84,7 @@ def test_two_rank_ipc_image_equals_single_rank_image(tmp_path):
                           timeout=600)
     res = json.load(open(out))
     print(res)
-    assert len(res) == 6
+    assert len(res) == 8
     for key, r in res.items():
         assert r["ok"], (key, r)
 
