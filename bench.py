@@ -90,6 +90,10 @@ def parse():
                          "rt_finalize_peers_barrier_async: the ranks meet through arrival words in peer memory, no collective call); "
                          "fused_nccl_barriers = the same kernel between two NCCL all-reduces of a scalar (round 1); "
                          "nccl = one torch.distributed reduce to rank 0 + rt_finalize")
+    ap.add_argument("--split", default="pixels", choices=["pixels", "spp"],
+                    help="N > 1: pixels = every rank renders all samples of its interleaved 128-pixel groups (rt_set_pixel_split; bit-identical "
+                         "picture, work items as long as on one GPU); spp = every rank renders its share of the samples of the whole frame "
+                         "(north_star's split, round 1)")
     ap.add_argument("--no-heads", action="store_true", help="RT_HEAD_OFF: trace every segment of every sample (A/B of the path-head memoisation)")
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS),
                     help="BASELINE.json configs; the driver's default (and the headline) is c2")
@@ -282,7 +286,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     import torch.distributed as dist
     sys.path.insert(0, PKG)
     import rtb200
-    from rtb200.multigpu import PeerFinalize, reduce_to_rank0, sample_range, split_image_check
+    from rtb200.multigpu import PeerFinalize, SharedHostImage, reduce_to_rank0, sample_range, split_image_check
 
     W, H, depth = cfg["W"], cfg["H"], cfg["depth"]
     arith = rtb200.ARITH_FAST if a.arith == "fast" else rtb200.ARITH_STRICT
@@ -302,7 +306,11 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         ctx.set_accum_device_buffer(accum.data_ptr(), accum.numel() * 4)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     peers = PeerFinalize(ctx, stream_ordered=True, device_barrier=(a.reduce == "fused")) if fused else None
-    first, n_mine = sample_range(spp, world, rank)
+    if world > 1 and a.split == "pixels":
+        first, n_mine = 0, spp
+        ctx.set_pixel_split(world, rank)
+    else:
+        first, n_mine = sample_range(spp, world, rank)
 
     def exchange(total_spp):
         if fused:
@@ -319,7 +327,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         torch.cuda.synchronize()
 
     # N > 1: the picture of the real multi-process path (IPC peer buffers / NCCL) against rank 0 alone, before anything is timed
-    check = split_image_check(ctx, cam, min(spp, 16 * world), world, rank, exchange) if world > 1 else None
+    check = split_image_check(ctx, cam, min(spp, 16 * world), world, rank, exchange, split=a.split) if world > 1 else None
 
     queries_steps = []
 
@@ -376,24 +384,26 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         work = ctx.work_counts()
         ctx.set_work_counting(False)
 
-    # ---- end to end through the C ABI with HOST buffers: every step uploads scene, textures, table (pinned
-    # host memory -> device), renders, reduces, finalizes and reads the image back to the host.
-    img_pinned = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()   # the caller's host image buffer (pinned, like the inputs)
-    img_host = img_pinned.numpy()
+    # ---- end to end through the C ABI with HOST buffers: every step uploads scene, textures, table (pinned host memory ->
+    # device), renders, and the exchange / finalize step stores the picture straight into the caller's page-locked HOST image
+    # (rt_set_finalize_target; N > 1: one shared host image, every rank writes its rows over its own PCIe link).
+    host_image = SharedHostImage(H, W, world, rank)
+    img_host = host_image.array
     tex_pinned = torch.from_numpy(tex).pin_memory()
     table_pinned = torch.from_numpy(table).pin_memory()
     h2d = tex_pinned.numel() * 4 + table_pinned.numel() * 4 + sum(v.nbytes for v in arr.values()) + 48
-    d2h = img_host.nbytes if rank == 0 else 0
+    d2h = img_host.nbytes                        # the whole picture crosses PCIe once per step (1/N of it per rank)
 
     def e2e_step():
         ctx.upload_textures(tex_pinned.numpy()); ctx.upload_scene(arr); ctx.set_random_table(table_pinned.numpy())
         r, _ = step()
-        if rank == 0:
-            ctx.read_image(img_host)
+        stream.synchronize()                     # rank 0: behind the last rank barrier, i.e. every rank's rows are in host memory
         return r
 
+    ctx.set_finalize_target(host_image.ptr, host_image.nbytes)
     e2e_step()
     sync_all()
+    e2e_image_ok = bool(img_host[..., 3].min() == 1.0 and img_host[..., :3].max() > 0.1) if rank == 0 else True
     t0 = time.perf_counter()
     e2e_rays = 0
     e2e_steps = max(1, min(steps, 3))
@@ -401,6 +411,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
         e2e_rays += e2e_step()
     sync_all()
     e2e_s = time.perf_counter() - t0
+    ctx.set_finalize_target(None, 0)
     t2 = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
     if world > 1:
         m = t2.clone(); dist.all_reduce(m, op=dist.ReduceOp.MAX)
@@ -413,7 +424,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     # them when the image is read (bit-identical to one launch per call); RTB200_EAGER=1 is the reference's schedule, one launch
     # and one host round trip per sample, timed on fewer samples.
     api = None
-    if world == 1 and with_cpu_baseline is not None and cfg["name"] in ("c1", "c2"):
+    if world == 1 and cfg["name"] in ("c1", "c2"):
         def api_run(n_samples):
             ctx.invalidate_caches()
             t_a = time.perf_counter()
@@ -486,7 +497,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
             "steps": steps, "warmup": warmup, "ms_per_step": round(elapsed_ms / steps, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_block(cfg, spp_total=spp, spp_per_gpu=n_mine, arith=a.arith, rng=a.rng,
-                                   parallelism=("spp-split x%d + %s" % (world, ("fused peer-memory reduce+finalize, device-side rank barrier (rt_finalize_peers_barrier_async)" if a.reduce == "fused"
+                                   parallelism=("%s x%d + %s" % ("interleaved pixel-group split (all samples of a pixel on one GPU)" if a.split == "pixels" else "spp-split", world, ("fused peer-memory reduce+finalize, device-side rank barrier (rt_finalize_peers_barrier_async)" if a.reduce == "fused"
                                                                               else "fused peer-memory reduce+finalize between two NCCL barriers") if fused else "1 NCCL reduce"))
                                    if world > 1 else "single GPU",
                                    rays_per_step=int(rays_total / steps), path_heads=not a.no_heads, bvh_nodes=int(ctx.stats().bvh_nodes),
@@ -494,9 +505,9 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
                                    l2="flushed between steps (256 MiB memset); the scene is re-read from HBM by the first blocks of every step"),
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                    "what": "rt_upload_textures + rt_upload_scene + rt_set_random_table from pinned host memory, "
-                            "rt_render_samples, reduce, rt_finalize, rt_read_image to host, every step"},
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "host_image_complete": e2e_image_ok,
+                    "what": "rt_upload_textures + rt_upload_scene + rt_set_random_table from pinned host memory, rt_render_samples, exchange + "
+                            "finalize storing the picture straight into the caller's page-locked host image (rt_set_finalize_target), every step"},
             "gpu_launches": int(launches),
             "roofline": roofline,
         }
@@ -512,6 +523,7 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     if peers is not None:
         peers.close()
     ctx.close()
+    host_image.close()
     del flush, accum
     torch.cuda.empty_cache()
     return out

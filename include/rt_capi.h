@@ -106,6 +106,12 @@ int rt_get_params(rt_ctx* ctx, rt_params* params);
  * the terms of src/raytracer.cpp:137, which always enqueues the whole frame): pixels outside keep their contents, the
  * per-pixel RNG keys and primary rays are those of the full frame.  w <= 0 or h <= 0 restores the whole frame. */
 int rt_set_region(rt_ctx* ctx, int x0, int y0, int w, int h);
+/* Pixel-interleaved work split for several GPUs: the frame is cut into groups of four 8 x 4 pixel tiles (128 pixels, the
+ * unit a block of the render kernels owns) numbered in launch order; this context renders group g iff g % n_parts == part
+ * and leaves all other pixels untouched.  Every pixel keeps its full-frame primary ray, RNG keys and ALL its samples in
+ * sample order, so the parts of a frame rendered by different contexts add up to the single-context picture BIT FOR BIT
+ * (each pixel has exactly one non-zero contribution).  n_parts <= 1 restores the whole frame. */
+int rt_set_pixel_split(rt_ctx* ctx, int n_parts, int part);
 
 /* RayTracer::render (src/raytracer.cpp:127-144): sample_counter = 0, one sample, overwrites the image. */
 int rt_render(rt_ctx* ctx, const float camera[12]);
@@ -147,6 +153,13 @@ int rt_restore_accum(rt_ctx* ctx, const float* rgba, uint32_t samples_in_buffer)
 int rt_accum_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
 int rt_image_device_ptr(rt_ctx* ctx, void** device_ptr, size_t* bytes);
 int rt_set_accum_device_buffer(rt_ctx* ctx, void* device_ptr, size_t bytes);
+/* Make rt_finalize / rt_finalize_peers* store the (sqrt(mean), 1) image at a caller-supplied DEVICE-ACCESSIBLE address
+ * instead of the context's image buffer — typically page-locked host memory mapped into the device's address space
+ * (cudaHostRegister / cudaHostAlloc mapped): the finalize kernel then writes the picture straight into the caller's host
+ * image over PCIe, no staging copy.  With the sample / pixel split every rank maps the SAME host buffer (shared memory) and
+ * stores its rows through its own PCIe link, so the read-back of a frame is spread over all links of the box.
+ * NULL restores the image buffer.  The reference has no read-back at all (its image is a GL texture). */
+int rt_set_finalize_target(rt_ctx* ctx, void* device_accessible_ptr, size_t bytes);
 
 /* Fused reduce + finalize over NVLink peer memory (the exchange step of the sample split; the reference has no
  * multi-device code).  Every rank exports its accumulation buffer (and rank 0 its image) as CUDA IPC handles

@@ -105,7 +105,8 @@ struct rt_ctx {
     rt_params prm{30u, RT_RNG_TABLE, 0u, RT_ARITH_STRICT, RT_MESH_FIRST_FRONT, RT_ACCEL_AUTO, RT_HEAD_ON};
     uint32_t sample_counter = 0;
     int rx0 = 0, ry0 = 0, rx1 = 0, ry1 = 0;   // render region (rt_set_region); the whole frame by default
-    int head_region[4] = {0, 0, 0, 0};
+    int head_region[6] = {0, 0, 0, 0, 0, 0};
+    uint32_t split_n = 1, split_i = 0;        // pixel split (rt_set_pixel_split)
     int64_t max_texture_used = -1;   // highest texture layer referenced by a textured mesh
     // fast arithmetic: Exact primary-hit ids of the current (scene, camera, mesh rule), see ensure_certified()
     uint32_t* d_certify = nullptr;
@@ -139,6 +140,7 @@ struct rt_ctx {
     void* peer_image0 = nullptr;
     bool peer_opened[kMaxPeers] = {false};   // accum pointers obtained from cudaIpcOpenMemHandle
     bool peer_image_opened = false;
+    float4* finalize_target = nullptr;        // rt_set_finalize_target: where rt_finalize* store the image instead of the image buffer
     bool peer_flags_ok = false;               // peers were opened through CUDA IPC: every buffer carries its flag words
     uint32_t peer_epoch = 0;
     uint32_t* d_barrier_timeout = nullptr;
@@ -444,7 +446,7 @@ int ensure_certified(rt_ctx* c, const float* cam) {
 int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
     *rebuilt = false;
     const bool bvh = c->bvh.n_leaves != 0;
-    const int region[4] = {c->rx0, c->ry0, c->rx1, c->ry1};
+    const int region[6] = {c->rx0, c->ry0, c->rx1, c->ry1, (int)c->split_n, (int)c->split_i};
     if (c->head_valid && c->head_mesh_mode == c->prm.mesh_mode && c->head_depth == c->prm.max_depth && c->head_bvh == bvh &&
         std::memcmp(c->head_cam, cam, 48) == 0 && std::memcmp(c->head_region, region, sizeof region) == 0)
         return RT_OK;
@@ -655,6 +657,14 @@ int rt_set_region(rt_ctx* c, int x0, int y0, int w, int h) {
     c->rx0 = x0; c->ry0 = y0; c->rx1 = x0 + w; c->ry1 = y0 + h;
     return RT_OK;
 }
+int rt_set_pixel_split(rt_ctx* c, int n_parts, int part) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    FLUSH(c);
+    if (n_parts <= 1) { c->split_n = 1; c->split_i = 0; return RT_OK; }
+    if (part < 0 || part >= n_parts) return fail(RT_ERR_INVALID, "rt_set_pixel_split: part %d of %d", part, n_parts);
+    c->split_n = (uint32_t)n_parts; c->split_i = (uint32_t)part;
+    return RT_OK;
+}
 int rt_set_work_counting(rt_ctx* c, int on) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     c->count_work = on != 0;
@@ -757,7 +767,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.sc = c->sc; L.tex = c->tex; L.table = c->d_table;
     std::memcpy(L.cam, cam, 12 * sizeof(float));
     L.W = c->W; L.H = c->H; L.first = first; L.n = n; L.depth = c->prm.max_depth;
-    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1;
+    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1; L.split_n = c->split_n; L.split_i = c->split_i;
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
@@ -905,7 +915,7 @@ int rt_finalize(rt_ctx* c, uint32_t spp) {
     if (spp == 0) return fail(RT_ERR_INVALID, "rt_finalize: spp must be > 0");
     FLUSH(c);
     Guard g(c);
-    CU(launch_finalize(c->d_accum, c->d_image, c->W * c->H, spp, c->stream));
+    CU(launch_finalize(c->d_accum, c->finalize_target ? c->finalize_target : c->d_image, c->W * c->H, spp, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->stats.kernel_launches += 1;
     return RT_OK;
@@ -964,6 +974,14 @@ int rt_image_device_ptr(rt_ctx* c, void** p, size_t* bytes) {
     FLUSH(c);
     *p = c->d_image;
     if (bytes) *bytes = (size_t)c->W * c->H * sizeof(float4);
+    return RT_OK;
+}
+int rt_set_finalize_target(rt_ctx* c, void* p, size_t bytes) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (!p) { c->finalize_target = nullptr; return RT_OK; }
+    if (bytes < (size_t)c->W * c->H * sizeof(float4)) return fail(RT_ERR_INVALID, "finalize target too small");
+    if (((uintptr_t)p & 15u) != 0) return fail(RT_ERR_INVALID, "finalize target must be 16-byte aligned");
+    c->finalize_target = (float4*)p;
     return RT_OK;
 }
 int rt_set_accum_device_buffer(rt_ctx* c, void* p, size_t bytes) {
@@ -1059,7 +1077,7 @@ static int finalize_peers(rt_ctx* c, uint32_t spp, bool sync, bool barriers) {
     Guard g(c);
     PeerFinalize P{};
     for (int r = 0; r < c->peer_n; ++r) P.accum[r] = (const float4*)c->peer_accum[r];
-    P.image = (float4*)c->peer_image0;
+    P.image = c->finalize_target ? c->finalize_target : (float4*)c->peer_image0;
     P.n_ranks = c->peer_n;
     const long long px = (long long)c->W * c->H;
     P.first_pixel = (int)(px * c->peer_rank / c->peer_n);

@@ -82,6 +82,7 @@ struct TraceLaunch {
     float cam[12];             // src/camera.cpp:94-118
     int W, H;
     int rx0, ry0, rx1, ry1;    // render region [rx0, rx1) x [ry0, ry1) of the frame (rt_set_region); pixels outside are untouched
+    uint32_t split_n, split_i; // pixel split (rt_set_pixel_split): slot group g (kTraceThreads slots = four 8 x 4 tiles) is rendered iff g % split_n == split_i
     uint32_t first, n;         // samples [first, first + n)
     uint32_t depth;
     uint32_t rng_mode, seed, accum_mode, mesh_mode;
@@ -116,6 +117,7 @@ struct HeadLaunch {
     float cam[12];
     int W, H;
     int rx0, ry0, rx1, ry1;    // render region: slots outside it are flagged kHeadDead
+    uint32_t split_n, split_i; // pixel split: slot groups of other parts are flagged kHeadDead
     uint32_t depth, mesh_mode;
     DevBvh bvh;
     float4* rec;               // 4 x n_slots

@@ -231,15 +231,27 @@ __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 
 //      reports hits on spheres the ray passes at up to sqrt(a - 1) b_u (found by tests/test_gpu_crops.py: 6 % of the
 //      pixels of the C5 crop differed before this was handled; the default scene's few big spheres never showed it).
 // So every box that can hold a sphere or lens is inflated, before the slab test, by slack x (an upper bound of the
-// distance from the ray origin to its farthest corner), slack = ray_slack(d) >= sqrt(7e-7 max(1, a) + max(a - 1, 0)), 1e-3 for a unit direction.
+// distance from the ray origin to its farthest corner), slack = ray_slack(d).slack >= sqrt(7e-7 max(1, a) + max(a - 1, 0)), 1e-3 for a unit direction.
 // Twelve more instructions per box; triangle-only nodes (BvhNode::flags == 0) do not need it in the fast arm — Moller-
 // Trumbore is exact in any parametrisation.
 #define RT_SLAB_SLACK 1.0e-3f
-__device__ __forceinline__ float ray_slack(V3 d) {
-    // shell^2 <= 7e-7 max(1, a) D^2 (rounding of dis) + max(a - 1, 0) b_u^2 (flare), b_u <= D; 2 % margin.  A normalised
-    // direction (|a - 1| <= 2.4e-7) gets exactly the round-1 slack of 1e-3.
+// Per-ray constants of the box tests.  slack: rounding shell of the sphere test, 1e-3 max(1, |d|) (exactly the round-1 slack
+// for a normalised direction).  sqa != 0 marks a FLARED ray (a - 1 > 3e-6), sqa = +-sqrt(a):
+//   sqa > 0  the scene has no lens: boxes are tested with slab_flared below;
+//   sqa < 0  a lens may be inside any flagged box (its two spheres' centres are NOT inside its box, so the bounds below do not
+//            hold): every flagged box is inflated by the full flare, nothing is pruned by distance — slow, but exact; only
+//            small test scenes take this path.
+struct RaySlack { float slack, sqa; };
+__device__ __forceinline__ RaySlack ray_slack(V3 d, bool lens_free = true) {
     const float a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
-    return fmaxf(RT_SLAB_SLACK, 1.02f * sqrtf(fmaf(7e-7f, fmaxf(1.0f, a), fmaxf(a - 1.0f, 0.0f))));
+    RaySlack r;
+    const bool flared = !(a - 1.0f <= 3e-6f);                                // NaN counts as flared
+    // ordinary ray: shell^2 <= (7e-7 max(1, a) + max(a - 1, 0)) D^2, 2 % margin; flared ray: the shell of Moller-Trumbore only
+    // (the spheres have their own test, slab_flared)
+    r.slack = flared ? RT_SLAB_SLACK * fmaxf(1.0f, sqrtf(a)) : fmaxf(RT_SLAB_SLACK, 1.02f * sqrtf(fmaf(7e-7f, fmaxf(1.0f, a), fmaxf(a - 1.0f, 0.0f))));
+    r.sqa = flared ? ((lens_free && a < 1e4f) ? sqrtf(a) : -sqrtf(fminf(a, 1e30f))) : 0.0f;
+    if (!(r.sqa == r.sqa)) { r.sqa = -1e15f; r.slack = RT_SLAB_SLACK; }
+    return r;
 }
 template <bool ROBUST>
 __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK) {
@@ -255,12 +267,68 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
     return t_near <= t_far && t_near <= t_best;
 }
+// Box test of a FLARED ray (cold path; 8 % of the queries of C5, none of the default scene).  The accepted hits of such a ray
+// are not near the spheres they belong to (t0 = b - sqrt(dis) of an aligned sphere at distance L is ~0.6 L / |d| for a = 1.3)
+// and lie in a cone around the ray, so the slab test neither bounds their parameter nor decides whether a box matters.
+// Both answers follow from the test itself.  For a sphere of radius r <= rho whose centre lies in the box, at distance L
+// from the origin (L_min <= L <= L_max), with b = oc.d <= b_max = max over the box:
+//   accepted        =>  c = L^2 - r^2 < 0 (origin inside)  or  b > 0 and b^2 > c - (rounding of dis, <= 1.4e-6 a L^2)
+//   its parameter   t0 >= sqrt(a) L - sqrt((a - 1) L^2 + r^2)      (minimum over b, at b = sqrt(a) L; grows with L, falls with r)
+// rho = half the smallest extent of the box (a sphere inside a box is no larger).  The lower bound orders the children and
+// prunes against the best hit, which keeps a flared ray as local as any other; without the two tests every box of the tree
+// passed (a step of C5 went from 0.2 s to 44 s).  Triangles in the same subtree are exact in any parametrisation: the
+// ordinary inflated slab decides for them, and the box passes if either test passes.
+static __device__ __noinline__ bool slab_flared(float lx, float ly, float lz, float hx, float hy, float hz, float ox, float oy, float oz,
+                                                float dx_, float dy_, float dz_, float ix, float iy, float iz, float t_best, float slack, float sqa,
+                                                bool curved, float* t_near_out) {
+    const float lo[3] = {lx, ly, lz}, hi[3] = {hx, hy, hz};
+    const V3 o = mk(ox, oy, oz), inv = mk(ix, iy, iz);
+    float t_tri;
+    bool pass = slab<true>(lo, hi, o, inv, t_best, t_tri, slack);          // triangles (and the a <= 1 view of spheres)
+    float t_near = pass ? t_tri : 3.0e38f;
+    if (curved) {
+        const float l0 = lx - ox, h0 = hx - ox, l1 = ly - oy, h1 = hy - oy, l2 = lz - oz, h2 = hz - oz;
+        const float ex = fmaxf(fmaxf(l0, -h0), 0.0f), ey = fmaxf(fmaxf(l1, -h1), 0.0f), ez = fmaxf(fmaxf(l2, -h2), 0.0f);
+        const float Lmin2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+        const float Lmax2 = fmaf(fmaxf(fabsf(l0), fabsf(h0)), fmaxf(fabsf(l0), fabsf(h0)),
+                                 fmaf(fmaxf(fabsf(l1), fabsf(h1)), fmaxf(fabsf(l1), fabsf(h1)), fmaxf(fabsf(l2), fabsf(h2)) * fmaxf(fabsf(l2), fabsf(h2))));
+        const float rho = 0.5f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2), rho2 = rho * rho;
+        const float a = sqa * sqa;
+        const float bmax = fmaxf(l0 * dx_, h0 * dx_) + fmaxf(l1 * dy_, h1 * dy_) + fmaxf(l2 * dz_, h2 * dz_);
+        const float c_min = Lmin2 - rho2;
+        const bool sph = c_min <= 0.0f || (bmax > 0.0f && fmaf(bmax, bmax * 1.0002f, 3e-6f * a * Lmax2) >= c_min * 0.9998f);
+        if (sph) {
+            float lb = 0.0f;
+            if (c_min > 0.0f) {
+                const float L = sqrtf(Lmin2);
+                // 0.998: covers the rounding shell of the reference's test (<= 8.5e-4 sqrt(a) L in t) and this arithmetic
+                lb = fmaxf(fmaf(0.998f * sqa, L, -1.0001f * sqrtf(fmaf(a - 1.0f, Lmin2, rho2))), 0.0f);
+            }
+            if (lb <= t_best) { pass = true; t_near = fminf(t_near, lb); }
+        }
+    }
+    *t_near_out = t_near;
+    return pass;
+}
+// One child box of a node in the robust path: ordinary rays take the inflated slab, flared rays the cold routine above.
+__device__ __forceinline__ bool slab_robust(const float lo[3], const float hi[3], V3 o, V3 d, V3 inv, float t_best, float& t_near,
+                                            const RaySlack rs, bool curved) {
+    if (rs.sqa == 0.0f) return slab<true>(lo, hi, o, inv, t_best, t_near, rs.slack);
+    if (rs.sqa < 0.0f) {                                                   // flared, lenses possible: full flare inflation, no distance pruning
+        const float a = rs.sqa * rs.sqa;
+        float tn;
+        const bool pass = slab<true>(lo, hi, o, inv, 3.0e38f, tn, curved ? fmaxf(rs.slack, 1.02f * sqrtf(fmaf(7e-7f, a, a - 1.0f))) : rs.slack);
+        t_near = curved ? 0.0f : tn;
+        return pass && t_near <= t_best;
+    }
+    return slab_flared(lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_best, rs.slack, rs.sqa, curved, &t_near);
+}
 template <class A>
 __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __restrict__ S, const DevBvh& bvh, V3 o, V3 d, Hit& best) {
     if (bvh.n_leaves == 0u) return;
     if (bvh.root < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~bvh.root), o, d, best); return; }
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    const float slack = ray_slack(d);
+    const RaySlack rs = ray_slack(d, sc.n_len == 0u);
     int stack[kBvhStack];
     int sp = 0, node = bvh.root;
     for (;;) {
@@ -269,7 +337,8 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
         const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
-        bool h0 = slab<true>(lo0, hi0, o, inv, best.t, t0, slack), h1 = slab<true>(lo1, hi1, o, inv, best.t, t1, slack);
+        const uint32_t fl = __float_as_uint(n2.w);
+        bool h0 = slab_robust(lo0, hi0, o, d, inv, best.t, t0, rs, (fl & 1u) != 0u), h1 = slab_robust(lo1, hi1, o, d, inv, best.t, t1, rs, (fl & 2u) != 0u);
         if (h0 && c0 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c0), o, d, best); h0 = false; }
         if (h1 && c1 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c1), o, d, best); h1 = false; }
         if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
@@ -667,7 +736,8 @@ __device__ __forceinline__ void trace_body(const TraceLaunch& p, float4* smem) {
     const int tile = blockIdx.x * (kTraceThreads / 32) + warp;
     const int x = (tile % tiles_x) * 8 + (lane & 7);
     const int y = (tile / tiles_x) * 4 + (lane >> 3);
-    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;   // the region lies inside the frame
+    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1 &&   // the region lies inside the frame
+                      (p.split_n <= 1u || blockIdx.x % p.split_n == p.split_i);   // block = slot group of the pixel split
 
     const V3 cam_o = mk(p.cam[0], p.cam[1], p.cam[2]);
     const V3 d0 = primary_dir<Exact>(p.cam, x, y, p.W, p.H);   // same primary ray in both arithmetic arms
@@ -732,7 +802,8 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
     const int tile = blockIdx.x * (kTraceThreads / 32) + warp;
     const int x = (tile % tiles_x) * 8 + (lane & 7);
     const int y = (tile / tiles_x) * 4 + (lane >> 3);
-    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;   // the region lies inside the frame
+    const bool live = x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1 &&   // the region lies inside the frame
+                      (p.split_n <= 1u || blockIdx.x % p.split_n == p.split_i);   // block = slot group of the pixel split
 
     const V3 cam_o = mk(p.cam[0], p.cam[1], p.cam[2]);
     const V3 d0 = primary_dir<Exact>(p.cam, x, y, p.W, p.H);
@@ -753,7 +824,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
 
     Hit h;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    float slack = RT_SLAB_SLACK;
+    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f;
     int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false;
@@ -763,7 +834,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
         if (traversing && node < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~node), o, d, h); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-        slack = ray_slack(d);
+        rs = ray_slack(d, p.sc.n_len == 0u);
     };
     bool has_ray = k < k_end;
     if (has_ray) start_ray();
@@ -776,7 +847,8 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
-                bool h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, slack), h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, slack);
+                const uint32_t fl = __float_as_uint(n2.w);
+                bool h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u), h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
                 if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
                 if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
                 if (h0 && h1) {
@@ -858,7 +930,8 @@ __device__ __forceinline__ void head_body(const HeadLaunch& p, float4* smem) {
     const uint32_t slot = blockIdx.x * kTraceThreads + threadIdx.x;
     int x, y;
     slot_pixel(slot, p.W, x, y);
-    const bool live = slot < p.n_slots && x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1;
+    const bool live = slot < p.n_slots && x >= p.rx0 && x < p.rx1 && y >= p.ry0 && y < p.ry1 &&
+                      (p.split_n <= 1u || blockIdx.x % p.split_n == p.split_i);
     uint32_t seg = 0u;
     V3 o = mk(p.cam[0], p.cam[1], p.cam[2]), d = primary_dir<Exact>(p.cam, x, y, p.W, p.H), out = mk(1.0f, 1.0f, 1.0f);
     uint32_t i = 0u, mat_id = 0u;
@@ -1079,7 +1152,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    float slack = RT_SLAB_SLACK;
+    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f;
     int sp = 0, node = 0;
     bool traversing = false, has_ray = false, have_result = false, exhausted = false;
     auto push = [&](int v) {
@@ -1095,7 +1168,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         sp = 0; node = p.bvh.root; traversing = p.bvh.n_leaves > 0u;
         if (traversing && node < 0) { bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~node), o, d, h, &wc); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-        slack = ray_slack(d);
+        rs = ray_slack(d, p.sc.n_len == 0u);
         have_result = true;
     };
 
@@ -1161,7 +1234,8 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 if (RT_BVH_FLAG_SLAB && !A::kExact && __float_as_uint(n2.w) == 0u) {
                     h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
                 } else {
-                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, slack); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, slack);
+                    const uint32_t fl = __float_as_uint(n2.w);
+                    h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
                 }
                 int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
                 if (l0 == 0) { l0 = l1; l1 = 0; }

@@ -18,7 +18,7 @@ extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_MIN_BLOCKS) k_tra
     trace_tail_body<Fused>(p, smem);
 }
 #ifndef RT_BVH_MIN_BLOCKS
-#define RT_BVH_MIN_BLOCKS 8
+#define RT_BVH_MIN_BLOCKS 7
 #endif
 extern "C" __global__ void __launch_bounds__(kTraceThreads, RT_BVH_MIN_BLOCKS) k_trace_tail_fast_bvh(const __grid_constant__ TraceLaunch p) {
     trace_tail_bvh_body<Fused, false>(p);

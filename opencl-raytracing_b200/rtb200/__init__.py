@@ -67,13 +67,13 @@ def lib():
         "rt_create": [ci, ci, ci, C.POINTER(vp)], "rt_destroy": [vp], "rt_set_stream": [vp, vp],
         "rt_upload_scene": [vp, C.POINTER(SceneDesc)], "rt_upload_textures": [vp, vp, ci, ci, ci],
         "rt_make_random_table": [u32, vp], "rt_set_random_table": [vp, vp, u32],
-        "rt_set_region": [vp, ci, ci, ci, ci], "rt_set_work_counting": [vp, ci], "rt_get_work_counts": [vp, vp], "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
+        "rt_set_region": [vp, ci, ci, ci, ci], "rt_set_pixel_split": [vp, ci, ci], "rt_set_work_counting": [vp, ci], "rt_get_work_counts": [vp, vp], "rt_set_params": [vp, C.POINTER(Params)], "rt_get_params": [vp, C.POINTER(Params)],
         "rt_render": [vp, vp], "rt_render_again": [vp, vp], "rt_render_samples": [vp, vp, u32, u32, u32],
         "rt_clear_accum": [vp], "rt_invalidate_caches": [vp], "rt_finalize": [vp, u32], "rt_read_image": [vp, vp], "rt_read_accum": [vp, vp],
         "rt_read_primary_ids": [vp, vp, vp, vp], "rt_restore_image": [vp, vp, u32], "rt_restore_accum": [vp, vp, u32], "rt_get_stats": [vp, C.POINTER(Stats)],
         "rt_accum_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_image_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
-        "rt_set_accum_device_buffer": [vp, vp, C.c_size_t],
+        "rt_set_accum_device_buffer": [vp, vp, C.c_size_t], "rt_set_finalize_target": [vp, vp, C.c_size_t],
         "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
         "rt_ipc_export": [vp, vp, vp], "rt_ipc_open_peers": [vp, ci, ci, vp, vp],
         "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_finalize_peers_async": [vp, u32], "rt_finalize_peers_barrier_async": [vp, u32], "rt_peer_barrier_status": [vp, C.POINTER(ci)], "rt_close_peers": [vp],
@@ -227,6 +227,10 @@ class Context:
         """Render only pixels [x0, x0+w) x [y0, y0+h); w <= 0 restores the whole frame."""
         _check(self.L.rt_set_region(self.h, x0, y0, w, h))
 
+    def set_pixel_split(self, n_parts=1, part=0):
+        """Render only the pixel groups g with g % n_parts == part (128-pixel groups in launch order)."""
+        _check(self.L.rt_set_pixel_split(self.h, n_parts, part))
+
     def set_work_counting(self, on):
         _check(self.L.rt_set_work_counting(self.h, 1 if on else 0))
 
@@ -308,6 +312,10 @@ class Context:
 
     def set_accum_device_buffer(self, ptr, nbytes):
         _check(self.L.rt_set_accum_device_buffer(self.h, ptr, nbytes))
+
+    def set_finalize_target(self, ptr, nbytes):
+        """rt_finalize / rt_finalize_peers* write the image to this device-accessible address (e.g. mapped pinned host memory)."""
+        _check(self.L.rt_set_finalize_target(self.h, ptr, nbytes))
 
     def ipc_export(self):
         """-> (accum handle, image handle), 64 bytes each (CUDA IPC)."""

@@ -1,4 +1,12 @@
-"""rtb200.multigpu — the sample split across the GPUs of one box (one process per GPU).
+"""rtb200.multigpu — splitting one render job across the GPUs of one box (one process per GPU).
+
+Two splits of the independent units (pixel-samples):
+  "spp"     (north_star) rank r renders the global sample indices [r*spp/world, (r+1)*spp/world) of the WHOLE frame;
+  "pixels"  rank r renders ALL samples of the interleaved 128-pixel groups g with g % world == r (rt_set_pixel_split):
+            per-lane work items stay as long as on one GPU (the kernel's efficiency depends on that), nothing is computed
+            twice except the path heads of the owned pixels, and the summed picture is bit-identical to one GPU's.
+Either way every rank holds a linear-sum buffer and ONE exchange step produces the image on rank 0.
+
 
 The path shards by independent units: rank r of `world` renders the global sample indices
 [r*spp/world, (r+1)*spp/world) of the whole frame into a private linear-sum buffer (RT_ACCUM_SUM); the only
@@ -68,17 +76,20 @@ class PeerFinalize:
         self.ctx.close_peers()
 
 
-def split_image_check(ctx, cam, spp, world, rank, finalize_split, group=None):
+def split_image_check(ctx, cam, spp, world, rank, finalize_split, group=None, split="spp"):
     """Correctness of the real multi-process path: the `world`-rank picture (every rank renders its global sample range
     into its linear-sum buffer, finalize_split(spp) = the exchange step: PeerFinalize.finalize or reduce_to_rank0 +
     rt_finalize on rank 0) against the same job rendered by rank 0 alone.  The RNG is keyed by global sample indices, so
-    the two differ by float summation order only.  Collective: every rank calls it; rank 0 gets
-    {"max_abs", "spp", "ok"}, the others None."""
+    the two differ by float summation order only.  split = "pixels": the ranks render interleaved pixel groups
+    (rt_set_pixel_split) with all samples each — every pixel then has exactly one contribution and the pictures must be
+    IDENTICAL.  Collective: every rank calls it; rank 0 gets {"max_abs", "spp", "ok"}, the others None."""
     import numpy as np
     import torch
     import torch.distributed as dist
     from . import ACCUM_SUM
-    first, n = sample_range(spp, world, rank)
+    first, n = sample_range(spp, world, rank) if split == "spp" else (0, spp)
+    if split == "pixels":
+        ctx.set_pixel_split(world, rank)
     ctx.clear_accum()
     ctx.render_samples(cam, first, n, ACCUM_SUM)
     finalize_split(spp)
@@ -87,14 +98,67 @@ def split_image_check(ctx, cam, spp, world, rank, finalize_split, group=None):
         dist.barrier(group=group)
     out = None
     if rank == 0:
-        split = ctx.read_image().copy()
+        split_img = ctx.read_image().copy()
+        ctx.set_pixel_split(1, 0)
         ctx.clear_accum()
         ctx.render_samples(cam, 0, spp, ACCUM_SUM)
         ctx.finalize(spp)
         single = ctx.read_image()
-        max_abs = float(np.abs(split[..., :3] - single[..., :3]).max())
-        out = {"max_abs": max_abs, "spp": int(spp), "tolerance": 2e-6,
-               "ok": bool(max_abs <= 2e-6 and np.all(split[..., 3] == 1.0) and float(single[..., :3].max()) > 0.1)}
+        max_abs = float(np.abs(split_img[..., :3] - single[..., :3]).max())
+        tol = 2e-6 if split == "spp" else 0.0
+        out = {"max_abs": max_abs, "spp": int(spp), "tolerance": tol, "split": split,
+               "ok": bool(max_abs <= tol and np.all(split_img[..., 3] == 1.0) and float(single[..., :3].max()) > 0.1)}
+        if split == "pixels":
+            ctx.set_pixel_split(world, rank)
     if world > 1:
         dist.barrier(group=group)
     return out
+
+
+class SharedHostImage:
+    """One host image (H x W x 4 float32) that EVERY rank's finalize kernel can store into: POSIX shared memory created by
+    rank 0, attached by the others, page-locked and mapped into each rank's device address space (cudaHostRegister).  With
+    rt_set_finalize_target every rank writes its rows of the picture straight to the host over its own PCIe link — the
+    read-back of a frame uses all links of the box instead of rank 0's alone.  world == 1: ordinary pinned memory."""
+
+    def __init__(self, H, W, world=1, rank=0, group=None):
+        import numpy as np
+        import torch
+        self.shm, self.registered, self.nbytes = None, False, H * W * 16
+        if world == 1:
+            self.tensor = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+            self.array = self.tensor.numpy()
+            self.ptr = self.tensor.data_ptr()
+            return
+        import torch.distributed as dist
+        from multiprocessing import shared_memory
+        name = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=self.nbytes)
+            name[0] = self.shm.name
+        dist.broadcast_object_list(name, src=0, group=group)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=name[0])
+        self.array = np.ndarray((H, W, 4), dtype=np.float32, buffer=self.shm.buf)
+        self.ptr = self.array.ctypes.data
+        err = torch.cuda.cudart().cudaHostRegister(self.ptr, self.nbytes, 3)      # cudaHostRegisterPortable | cudaHostRegisterMapped
+        if int(err) != 0:
+            raise RuntimeError("cudaHostRegister of the shared host image failed: %s" % (err,))
+        self.registered = True
+        self.rank = rank
+        dist.barrier(group=group)
+
+    def close(self):
+        import torch
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.ptr)
+            self.registered = False
+        if self.shm is not None:
+            self.array = None
+            try:
+                self.shm.close()
+                if self.rank == 0:
+                    self.shm.unlink()
+            except Exception:
+                pass
+            self.shm = None

@@ -122,6 +122,7 @@ def test_counted_work_of_the_lbvh_kernel(table):
         ctx.upload_scene(arrays)
         ctx.set_random_table(table)
         ctx.set_params(max_depth=12, rng_mode=rt.RNG_COUNTER_TABLE, seed=1, arith=rt.ARITH_FAST, mesh_mode=rt.MESH_NEAREST)
+        ctx.render_samples(cam, 0, 1, rt.ACCUM_SUM)            # builds the path heads (their queries count once)
         ctx.clear_accum()
         ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
         plain, q_plain = ctx.read_accum().copy(), ctx.stats().queries_last
@@ -159,3 +160,34 @@ def test_failed_lbvh_build_is_an_error_not_a_half_built_tree(table, monkeypatch)
         monkeypatch.delenv("RTB200_TEST_FAIL_BVH_BUILD")
         ctx.render_samples(cam, 0, 2, rt.ACCUM_REFERENCE)
         assert ctx.stats().bvh_nodes == 1500 and np.isfinite(ctx.read_image()).all()
+
+
+def test_pixel_split_parts_add_up_bit_for_bit(scenes, table):
+    """rt_set_pixel_split: the parts of a frame (interleaved 128-pixel groups, all samples each) rendered one after the
+    other are disjoint, cover the frame, and their sum IS the single-context accumulation buffer — in both arms, with path
+    heads on and off, brute force and LBVH."""
+    import rtb200 as rt
+    from rtb200 import fixtures as fx
+    W, H, spp = 400, 236, 10
+    cam = fx.camera(60, W / H)
+    for arith, head, accel, mesh in ((rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT), (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT),
+                                     (rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_BVH, rt.MESH_NEAREST), (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_BVH, rt.MESH_NEAREST)):
+        with make_ctx(rt, scenes, "default", W, H, table, max_depth=12, arith=arith, rng_mode=rt.RNG_COUNTER_TABLE, seed=6, path_head=head,
+                      accel=accel, mesh_mode=mesh) as ctx:
+            ctx.clear_accum()
+            ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+            whole, rays_whole = ctx.read_accum().copy(), ctx.stats().rays_last
+            parts, rays = np.zeros_like(whole), 0
+            for n_parts in (3,):
+                for part in range(n_parts):
+                    ctx.set_pixel_split(n_parts, part)
+                    ctx.clear_accum()
+                    ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+                    a = ctx.read_accum()
+                    assert not (parts[..., 3] * a[..., 3]).any()            # disjoint
+                    parts += a
+                    rays += ctx.stats().rays_last
+            assert np.array_equal(bits(parts), bits(whole)) and rays == rays_whole
+            with pytest.raises(rt.RtError):
+                ctx.set_pixel_split(4, 4)
+            ctx.set_pixel_split(1, 0)

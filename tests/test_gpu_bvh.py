@@ -176,3 +176,36 @@ def test_bvh_deep_tree_equals_brute_force():
         iv, tv = v.trace_rays(rays)
     assert (ib != rt.ID_MISS).mean() > 0.1 and len(np.unique(ib)) > 100
     assert np.array_equal(ib, iv) and np.array_equal(bits(tb), bits(tv))
+
+
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+def test_bvh_equals_brute_force_for_non_unit_directions(arith):
+    """The reference's sphere test assumes |d| = 1 but is fed refracted, un-normalised directions (cl:386,428): for
+    |d|^2 = a > 1 it accepts p^2 < r^2 + (a - 1) b_u^2, i.e. brute force reports hits on spheres the ray merely passes
+    (found on the C5 crop).  The LBVH must return exactly those hits: random rays with a between 0.3 and 7
+    (and a just above 1) against the brute-force kernels on a scene small enough for shared memory — same id, same t bits —
+    with a dense field of small spheres so that the flare matters (a third of the winners are phantom hits)."""
+    import rtb200 as rt
+    from rtb200 import synth
+    arrays, info = synth.scene(n_spheres=480, mesh_subdiv=1, seed=11, sphere_box=((-6, -4, 2), (6, 1.2, 14)), radii=(0.03, 0.12))
+    rays = random_rays(80000, 6, box=((-7, -5, 0), (7, 1.4, 16)))
+    rng = np.random.RandomState(8)
+    a = np.concatenate([rng.uniform(0.3, 7.0, 50000), 1.0 + 10.0 ** rng.uniform(-6, -1, 30000)])
+    rays[:, 3:] *= np.sqrt(a)[:, None].astype(np.float32)
+    A = getattr(rt, "ARITH_" + arith.upper())
+    with ctx_for(rt, arrays, arith=A, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BRUTE) as b, \
+         ctx_for(rt, arrays, arith=A, mesh_mode=rt.MESH_NEAREST, accel=rt.ACCEL_BVH) as v:
+        ib, tb = b.trace_rays(rays)
+        iv, tv = v.trace_rays(rays)
+        assert b.stats().bvh_nodes == 0 and v.stats().bvh_nodes > 0
+    # phantom hits exist: winners whose sphere the ray misses geometrically
+    sph = arrays["spheres"].view(np.float32).reshape(-1, 8)
+    is_sph = (ib >> 28) == 1
+    idx = (ib[is_sph] & 0x0FFFFFFF).astype(np.int64)
+    o, d = rays[is_sph, :3].astype(np.float64), rays[is_sph, 3:].astype(np.float64)
+    u = d / np.linalg.norm(d, axis=1, keepdims=True)
+    oc = sph[idx, :3].astype(np.float64) - o
+    perp = np.sqrt(np.maximum((oc * oc).sum(1) - (oc * u).sum(1) ** 2, 0.0))
+    assert (perp > 1.01 * sph[idx, 4] + 1e-5).mean() > 0.05
+    assert np.array_equal(ib, iv)
+    assert np.array_equal(bits(tb), bits(tv))

@@ -52,6 +52,8 @@ def _main(out_path):
                 peers = PeerFinalize(ctx, stream_ordered=(mode == "fused_stream"), device_barrier=(mode == "fused_flags"))
                 fin = peers.finalize
             r = split_image_check(ctx, cam, 24, world, rank, fin)
+            rp = split_image_check(ctx, cam, 24, world, rank, fin, split="pixels")   # interleaved pixel groups: identical picture
+            ctx.set_pixel_split(1, 0)
             if mode == "fused_flags":
                 for _ in range(3):                      # the epochs keep counting: repeated rounds on the same contexts
                     r2 = split_image_check(ctx, cam, 24, world, rank, fin)
@@ -62,6 +64,7 @@ def _main(out_path):
                     r["ok"] = r["ok"] and not timed_out
             if rank == 0:
                 results["%s/%s" % (arith, mode)] = r
+                results["%s/%s/pixels" % (arith, mode)] = rp
             if mode != "nccl":
                 peers.close()
             ctx.close()
@@ -84,9 +87,11 @@ def test_two_rank_ipc_image_equals_single_rank_image(tmp_path):
                           timeout=600)
     res = json.load(open(out))
     print(res)
-    assert len(res) == 8
+    assert len(res) == 16
     for key, r in res.items():
         assert r["ok"], (key, r)
+        if key.endswith("/pixels"):
+            assert r["max_abs"] == 0.0, (key, r)
 
 
 if __name__ == "__main__":

@@ -3,7 +3,8 @@ nvdisasm -g line info.  Regions are found from the source file itself (function 
 attributed to the enclosing kernel-file line.  usage: sass_regions.py <ncu_sass.csv> <nvdisasm.sass> <kernel> [raw.csv]"""
 import csv, re, sys, collections
 ncu_csv, dis, kernel = sys.argv[1:4]
-SRC = "/root/repo/opencl-raytracing_b200/csrc/rt_kernels.cuh"
+import os
+SRC = os.environ.get("RT_SRC", "/root/repo/opencl-raytracing_b200/csrc/rt_kernels.cuh")   # the source the profiled library was built from
 src = open(SRC).read().split("\n")
 # region boundaries: lines starting a function definition
 marks = []
@@ -54,3 +55,16 @@ if len(sys.argv) > 4:
               "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
               "dram__bytes_read.sum", "dram__bytes_write.sum"):
         if n in h: print("  %-66s %s %s" % (n, rr[2][h.index(n)], rr[1][h.index(n)]))
+    stalls = []
+    for i, n in enumerate(h):
+        m = re.match(r"smsp__average_warps_issue_stalled_(.+)_per_issue_active.ratio", n)
+        if m:
+            try: stalls.append((float(rr[2][i]), m.group(1)))
+            except ValueError: pass
+    stalls.sort(reverse=True)
+    if stalls: print("  stalls per issue: " + ", ".join("%s %.2f" % (n, v) for v, n in stalls[:6]))
+    try:
+        a, e = float(rr[2][h.index("sm__cycles_active.avg")]), float(rr[2][h.index("sm__cycles_elapsed.avg")])
+        print("  SM active / elapsed cycles = %.3f" % (a / e))
+    except (ValueError, IndexError):
+        pass
