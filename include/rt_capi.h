@@ -218,7 +218,8 @@ int rt_write_tga(const char* path, const float* rgba, int width, int height);
  * brute-force operation count of kernels/raytracer.cl:322-360).  While counting is on, fast-arithmetic renders of LBVH
  * scenes go through an instrumented copy of the render kernel — same image, not to be timed — and rt_get_work_counts
  * returns, for the last render call: [0] node visits (two box tests each), leaf tests of [1] spheres, [2] lenses,
- * [3] triangles, [4] plane tests, [5] nearest-hit queries of the render kernel, [6..7] zero. */
+ * [3] triangles, [4] plane tests, [5] nearest-hit queries of the render kernel, [6] node visits made by flared rays
+ * (|d| != 1; their box test costs about three ordinary ones), [7] flared queries. */
 int rt_set_work_counting(rt_ctx* ctx, int on);
 int rt_get_work_counts(rt_ctx* ctx, uint64_t out[8]);
 

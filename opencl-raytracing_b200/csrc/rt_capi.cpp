@@ -468,7 +468,7 @@ int ensure_head(rt_ctx* c, const float* cam, bool* rebuilt) {
     L.sc = c->sc;
     std::memcpy(L.cam, cam, 48);
     L.W = c->W; L.H = c->H; L.depth = c->prm.max_depth; L.mesh_mode = c->prm.mesh_mode; L.bvh = dev_bvh(c);
-    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1;
+    L.rx0 = c->rx0; L.ry0 = c->ry0; L.rx1 = c->rx1; L.ry1 = c->ry1; L.split_n = c->split_n; L.split_i = c->split_i;
     L.key_mask = 0x3FFFu;
     if (const char* e = std::getenv("RTB200_HEAD_SORT")) L.key_mask = (uint32_t)std::strtoul(e, nullptr, 0);   // A/B: 0 = slot order
     L.rec = c->d_head_rec; L.flag = c->d_head_flag; L.key = c->d_head_key; L.n_slots = n_slots; L.segments = c->d_head_counts;

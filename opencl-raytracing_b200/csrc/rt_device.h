@@ -107,7 +107,7 @@ struct TraceLaunch {
     uint32_t* block_cost;
     const uint32_t* block_order;
     // Instrumented LBVH kernel (k_trace_tail_fast_bvh_count, untimed): [0] node visits (two box tests each), leaf tests of
-    // [1] spheres, [2] lenses, [3] triangles.  nullptr in the timed kernels.
+    // [1] spheres, [2] lenses, [3] triangles; [6] node visits of flared rays, [7] flared queries.  nullptr in the timed kernels.
     unsigned long long* work;
 };
 

@@ -199,7 +199,7 @@ __device__ __forceinline__ bool closer(float t, uint32_t id, const Hit& best) {
 // index followed by a dependent fetch from the scene's stream.
 // Work counters of the instrumented (untimed) LBVH render kernel: the numerator of the roofline of a BVH run is COUNTED
 // work, not the brute-force operation count.
-struct WorkCount { uint32_t nodes, sph, len, tri; };
+struct WorkCount { uint32_t nodes, sph, len, tri, flared_nodes, flared_queries; };
 template <class A, bool COUNT = false>
 __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 d, Hit& best, WorkCount* wc = nullptr) {
     const float4 r0 = __ldg(L), r1 = __ldg(L + 1), r2 = __ldg(L + 2), r3 = __ldg(L + 3);
@@ -278,36 +278,45 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
 // prunes against the best hit, which keeps a flared ray as local as any other; without the two tests every box of the tree
 // passed (a step of C5 went from 0.2 s to 44 s).  Triangles in the same subtree are exact in any parametrisation: the
 // ordinary inflated slab decides for them, and the box passes if either test passes.
+// `tri`: the subtree may hold triangles (scene-wide: the scene has any), `curved`: it may hold spheres.
+__device__ __forceinline__ bool slab_flared_core(const float lo[3], const float hi[3], V3 o, V3 d, V3 inv, float t_best, float slack, float sqa,
+                                                 bool curved, bool tri, float& t_near_out) {
+    bool pass = false;
+    float t_near = 3.0e38f;
+    if (tri || !curved) {                                                  // triangles: exact in any parametrisation
+        float t_tri;
+        pass = slab<true>(lo, hi, o, inv, t_best, t_tri, slack);
+        if (pass) t_near = t_tri;
+    }
+    if (curved) {
+        const float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
+        const float ex = fmaxf(fmaxf(l0, -h0), 0.0f), ey = fmaxf(fmaxf(l1, -h1), 0.0f), ez = fmaxf(fmaxf(l2, -h2), 0.0f);
+        const float Lmin2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+        const float mx = fmaxf(fabsf(l0), fabsf(h0)), my = fmaxf(fabsf(l1), fabsf(h1)), mz = fmaxf(fabsf(l2), fabsf(h2));
+        const float Lmax2 = fmaf(mx, mx, fmaf(my, my, mz * mz));
+        const float rho = 0.5f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2), rho2 = rho * rho;
+        const float a = sqa * sqa;
+        const float bmax = fmaxf(l0 * d.x, h0 * d.x) + fmaxf(l1 * d.y, h1 * d.y) + fmaxf(l2 * d.z, h2 * d.z);
+        const float c_min = Lmin2 - rho2;
+        if (c_min <= 0.0f || (bmax > 0.0f && fmaf(bmax, bmax * 1.0002f, 3e-6f * a * Lmax2) >= c_min * 0.9998f)) {
+            // lower bound of t; 0.998 covers the rounding shell of the reference's test (<= 8.5e-4 sqrt(a) L in t) and this
+            // arithmetic.  Boxes too large for a bound (c_min <= 0) are ordered by their distance: 1e-6 L <= 0.001 <= any t.
+            const float L = sqrtf(Lmin2);
+            float lb = 1e-6f * L;
+            if (c_min > 0.0f) lb = fmaxf(lb, fmaf(0.998f * sqa, L, -1.0001f * sqrtf(fmaf(a - 1.0f, Lmin2, rho2))));
+            if (lb <= t_best) { pass = true; t_near = fminf(t_near, lb); }
+        }
+    }
+    t_near_out = t_near;
+    return pass;
+}
 static __device__ __noinline__ bool slab_flared(float lx, float ly, float lz, float hx, float hy, float hz, float ox, float oy, float oz,
                                                 float dx_, float dy_, float dz_, float ix, float iy, float iz, float t_best, float slack, float sqa,
                                                 bool curved, float* t_near_out) {
     const float lo[3] = {lx, ly, lz}, hi[3] = {hx, hy, hz};
-    const V3 o = mk(ox, oy, oz), inv = mk(ix, iy, iz);
-    float t_tri;
-    bool pass = slab<true>(lo, hi, o, inv, t_best, t_tri, slack);          // triangles (and the a <= 1 view of spheres)
-    float t_near = pass ? t_tri : 3.0e38f;
-    if (curved) {
-        const float l0 = lx - ox, h0 = hx - ox, l1 = ly - oy, h1 = hy - oy, l2 = lz - oz, h2 = hz - oz;
-        const float ex = fmaxf(fmaxf(l0, -h0), 0.0f), ey = fmaxf(fmaxf(l1, -h1), 0.0f), ez = fmaxf(fmaxf(l2, -h2), 0.0f);
-        const float Lmin2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
-        const float Lmax2 = fmaf(fmaxf(fabsf(l0), fabsf(h0)), fmaxf(fabsf(l0), fabsf(h0)),
-                                 fmaf(fmaxf(fabsf(l1), fabsf(h1)), fmaxf(fabsf(l1), fabsf(h1)), fmaxf(fabsf(l2), fabsf(h2)) * fmaxf(fabsf(l2), fabsf(h2))));
-        const float rho = 0.5f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2), rho2 = rho * rho;
-        const float a = sqa * sqa;
-        const float bmax = fmaxf(l0 * dx_, h0 * dx_) + fmaxf(l1 * dy_, h1 * dy_) + fmaxf(l2 * dz_, h2 * dz_);
-        const float c_min = Lmin2 - rho2;
-        const bool sph = c_min <= 0.0f || (bmax > 0.0f && fmaf(bmax, bmax * 1.0002f, 3e-6f * a * Lmax2) >= c_min * 0.9998f);
-        if (sph) {
-            float lb = 0.0f;
-            if (c_min > 0.0f) {
-                const float L = sqrtf(Lmin2);
-                // 0.998: covers the rounding shell of the reference's test (<= 8.5e-4 sqrt(a) L in t) and this arithmetic
-                lb = fmaxf(fmaf(0.998f * sqa, L, -1.0001f * sqrtf(fmaf(a - 1.0f, Lmin2, rho2))), 0.0f);
-            }
-            if (lb <= t_best) { pass = true; t_near = fminf(t_near, lb); }
-        }
-    }
-    *t_near_out = t_near;
+    float tn;
+    const bool pass = slab_flared_core(lo, hi, mk(ox, oy, oz), mk(dx_, dy_, dz_), mk(ix, iy, iz), t_best, slack, sqa, curved, true, tn);
+    *t_near_out = tn;
     return pass;
 }
 // One child box of a node in the robust path: ordinary rays take the inflated slab, flared rays the cold routine above.
@@ -1149,12 +1158,13 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
     };
     uint32_t queries = 0u;
-    WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = 0u;
+    WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = wc.flared_nodes = wc.flared_queries = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
     RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f;
     int sp = 0, node = 0;
-    bool traversing = false, has_ray = false, have_result = false, exhausted = false;
+    bool traversing = false, has_ray = false, have_result = false, exhausted = false, flare_mode = false;
+    constexpr uint32_t kFlarePark = 12u;
     auto push = [&](int v) {
         if (sp < RT_BVH_SSTACK) sst[sp * kTraceThreads] = v;
         else if (sp < kBvhStack) lst[sp - RT_BVH_SSTACK] = v;
@@ -1169,6 +1179,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         if (traversing && node < 0) { bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~node), o, d, h, &wc); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
         rs = ray_slack(d, p.sc.n_len == 0u);
+        if (COUNT && rs.sqa != 0.0f) ++wc.flared_queries;
         have_result = true;
     };
 
@@ -1223,19 +1234,35 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
             }
         }
         for (;;) {                                           // ---- traversal: one node per trip
-            if (traversing) {
+            // Flared rays (rs.sqa != 0, slab_flared_core) need three times the instructions of an ordinary box test; mixed into
+            // ordinary trips every one of them would cost the warp a whole extra instruction stream (C5: 5 % of the queries,
+            // i.e. nearly every trip).  They are PARKED instead and traverse together in trips of their own (flare_mode, warp
+            // uniform): entered when kFlarePark lanes are parked or nothing else traverses, left when the last one is done.
+            {
+                const unsigned tf = __ballot_sync(RT_FULL, traversing && rs.sqa != 0.0f), tn = __ballot_sync(RT_FULL, traversing && rs.sqa == 0.0f);
+                if (!flare_mode) flare_mode = tf != 0u && (tn == 0u || (uint32_t)__popc(tf) >= kFlarePark);
+                else flare_mode = tf != 0u;
+            }
+            if (traversing && (rs.sqa != 0.0f) == flare_mode) {
                 const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
                 const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
                 bool h0, h1;
-                if (COUNT) ++wc.nodes;
-                if (RT_BVH_FLAG_SLAB && !A::kExact && __float_as_uint(n2.w) == 0u) {
+                if (COUNT) { ++wc.nodes; if (flare_mode) ++wc.flared_nodes; }
+                const uint32_t fl = __float_as_uint(n2.w);
+                if (flare_mode) {
+                    if (rs.sqa > 0.0f) {
+                        h0 = slab_flared_core(lo0, hi0, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 1u) != 0u, p.sc.n_tri != 0u, t0);
+                        h1 = slab_flared_core(lo1, hi1, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 2u) != 0u, p.sc.n_tri != 0u, t1);
+                    } else {
+                        h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
+                    }
+                } else if (RT_BVH_FLAG_SLAB && !A::kExact && fl == 0u) {
                     h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
                 } else {
-                    const uint32_t fl = __float_as_uint(n2.w);
-                    h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, rs.slack); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, rs.slack);
                 }
                 int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
                 if (l0 == 0) { l0 = l1; l1 = 0; }
@@ -1262,10 +1289,12 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     if (lane == 0u && queries) atomicAdd(p.queries, (unsigned long long)queries);
     if (COUNT) {
         const uint32_t a = __reduce_add_sync(RT_FULL, wc.nodes), b = __reduce_add_sync(RT_FULL, wc.sph),
-                       c = __reduce_add_sync(RT_FULL, wc.len), e = __reduce_add_sync(RT_FULL, wc.tri);
+                       c = __reduce_add_sync(RT_FULL, wc.len), e = __reduce_add_sync(RT_FULL, wc.tri),
+                       fn = __reduce_add_sync(RT_FULL, wc.flared_nodes), fq = __reduce_add_sync(RT_FULL, wc.flared_queries);
         if (lane == 0u && p.work) {
             atomicAdd(p.work + 0, (unsigned long long)a); atomicAdd(p.work + 1, (unsigned long long)b);
             atomicAdd(p.work + 2, (unsigned long long)c); atomicAdd(p.work + 3, (unsigned long long)e);
+            atomicAdd(p.work + 6, (unsigned long long)fn); atomicAdd(p.work + 7, (unsigned long long)fq);
         }
     }
 }

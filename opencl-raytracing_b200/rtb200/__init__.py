@@ -239,7 +239,7 @@ class Context:
         w = np.zeros(8, np.uint64)
         _check(self.L.rt_get_work_counts(self.h, w.ctypes.data))
         return dict(node_visits=int(w[0]), sphere_tests=int(w[1]), lens_tests=int(w[2]), triangle_tests=int(w[3]),
-                    plane_tests=int(w[4]), queries=int(w[5]))
+                    plane_tests=int(w[4]), queries=int(w[5]), flared_node_visits=int(w[6]), flared_queries=int(w[7]))
 
     @staticmethod
     def _cam(cam):

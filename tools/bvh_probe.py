@@ -43,7 +43,8 @@ def main():
                        grays_equiv=round(best["rays"] / best["ms"] / 1e6, 3), gqueries=round(best["queries"] / best["ms"] / 1e6, 3),
                        ms=round(best["ms"], 2), ms_trace=round(best["ms_trace"], 2),
                        nodes_per_query=round(wc["node_visits"] / q, 2), tri_per_query=round(wc["triangle_tests"] / q, 2),
-                       sph_per_query=round(wc["sphere_tests"] / q, 2), counts=wc)
+                       sph_per_query=round(wc["sphere_tests"] / q, 2), flared_frac=round(wc["flared_queries"] / q, 4),
+                       nodes_per_flared_query=round(wc["flared_node_visits"] / max(wc["flared_queries"], 1), 1), counts=wc)
             print(json.dumps(out), flush=True)
 
 
