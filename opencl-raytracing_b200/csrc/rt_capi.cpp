@@ -689,7 +689,27 @@ int rt_get_params(rt_ctx* c, rt_params* p) {
 // The strict arm keeps one item per pixel: its sums are added in sample order, like the oracle's.
 static int plan_chunks(rt_ctx* c, TraceLaunch& L) {
     L.chunks = 1; L.chunk_spp = L.n; L.partial = nullptr;
-    if (c->prm.arith != RT_ARITH_FAST || L.accum_mode != RT_ACCUM_SUM || L.bvh.n_leaves || L.head.n_stoch == 0) return RT_OK;
+    if (c->prm.arith != RT_ARITH_FAST || L.accum_mode != RT_ACCUM_SUM || L.head.n_stoch == 0) return RT_OK;
+    if (L.bvh.n_leaves) {
+        // LBVH kernel: items of kBvhChunkSpp samples (see trace_tail_bvh_body: a few pixels behind glass chains cost hundreds of
+        // times the average), at most 32 chunks of a pixel (the chunk sums take chunks x 16 B per stochastic pixel).
+        uint64_t chunk_spp = 2;
+        if (const char* e = std::getenv("RTB200_BVH_CHUNK_SPP")) chunk_spp = (uint64_t)std::max(1ll, std::atoll(e));
+        uint64_t chunks = std::min<uint64_t>((L.n + chunk_spp - 1u) / chunk_spp, 32u);
+        chunks = std::min<uint64_t>(chunks, (1ull << 31) / L.head.n_stoch);
+        if (chunks < 2) return RT_OK;
+        L.chunk_spp = (uint32_t)((L.n + chunks - 1u) / chunks);
+        L.chunks = (L.n + L.chunk_spp - 1u) / L.chunk_spp;
+        const size_t want = (size_t)L.chunks * L.head.n_stoch;
+        if (want > c->partial_cap) {
+            CU(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_partial); c->d_partial = nullptr; c->partial_cap = 0;
+            CU(cudaMalloc(&c->d_partial, want * sizeof(float4)));
+            c->partial_cap = want;
+        }
+        L.partial = c->d_partial;
+        return RT_OK;
+    }
     if (!c->sm_count) {
         int dev = 0;
         CU(cudaGetDevice(&dev));

@@ -19,6 +19,7 @@
 #include "rt_bvh.h"
 #include "rt_device.h"
 #include "rt_math.cuh"
+#include <algorithm>
 
 namespace rtb {
 
@@ -235,28 +236,42 @@ __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 
 // Twelve more instructions per box; triangle-only nodes (BvhNode::flags == 0) do not need it in the fast arm — Moller-
 // Trumbore is exact in any parametrisation.
 #define RT_SLAB_SLACK 1.0e-3f
-// Per-ray constants of the box tests.  slack: rounding shell of the sphere test, 1e-3 max(1, |d|) (exactly the round-1 slack
-// for a normalised direction).  sqa != 0 marks a FLARED ray (a - 1 > 3e-6), sqa = +-sqrt(a):
-//   sqa > 0  the scene has no lens: boxes are tested with slab_flared below;
-//   sqa < 0  a lens may be inside any flagged box (its two spheres' centres are NOT inside its box, so the bounds below do not
-//            hold): every flagged box is inflated by the full flare, nothing is pruned by distance — slow, but exact; only
-//            small test scenes take this path.
-struct RaySlack { float slack, sqa; };
+// Per-ray constants of the box tests (a = |d|^2):
+//   ordinary ray (a - 1 <= 3e-6)       slack = 1e-3 (the round-1 value), kappa = 1, sqa = 0: inflated slab, pruned by its entry.
+//   THIN flare (3e-6 < a - 1 <= RT_BVH_THIN_FLARE, scene without lenses)   stays in the ordinary code path: the box is inflated
+//       by the whole flare, slack >= sqrt(7e-7 a + (a - 1)), which for these rays is a few percent of the distance, and the
+//       entry parameter is turned into a valid lower bound of the hit parameter: the point of closest approach to an accepted
+//       sphere's centre (parameter t_c) lies inside the inflated box, and t0 >= sqrt(a)(sqrt(a) - sqrt(a - 1)) t_c - r, so
+//       t0 >= kappa * t_entry - rho with rho = half the smallest extent of the box (>= r of any sphere inside).
+//   WIDE flare: sqa = sqrt(a) > 0, boxes tested by slab_flared_core below (cone test + analytic bound), in trips of their own;
+//       sqa < 0  a lens may be inside any flagged box (its two spheres' centres are NOT inside its box, so none of the bounds
+//       holds): every flagged box is inflated by the full flare, nothing is pruned by distance — slow, but exact; only small
+//       test scenes take this path.
+#ifndef RT_BVH_THIN_FLARE
+#define RT_BVH_THIN_FLARE 1.0e-2f
+#endif
+struct RaySlack { float slack, sqa, kappa; };
 __device__ __forceinline__ RaySlack ray_slack(V3 d, bool lens_free = true) {
     const float a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
     RaySlack r;
     const bool flared = !(a - 1.0f <= 3e-6f);                                // NaN counts as flared
-    // ordinary ray: shell^2 <= (7e-7 max(1, a) + max(a - 1, 0)) D^2, 2 % margin; flared ray: the shell of Moller-Trumbore only
-    // (the spheres have their own test, slab_flared)
-    r.slack = flared ? RT_SLAB_SLACK * fmaxf(1.0f, sqrtf(a)) : fmaxf(RT_SLAB_SLACK, 1.02f * sqrtf(fmaf(7e-7f, fmaxf(1.0f, a), fmaxf(a - 1.0f, 0.0f))));
-    r.sqa = flared ? ((lens_free && a < 1e4f) ? sqrtf(a) : -sqrtf(fminf(a, 1e30f))) : 0.0f;
-    if (!(r.sqa == r.sqa)) { r.sqa = -1e15f; r.slack = RT_SLAB_SLACK; }
+    const bool thin = flared && lens_free && a - 1.0f <= RT_BVH_THIN_FLARE;
+    // ordinary and thin: shell^2 <= (7e-7 max(1, a) + max(a - 1, 0)) D^2, 2 % margin; wide flare: the shell of Moller-Trumbore
+    // only (the spheres have their own test, slab_flared_core)
+    r.slack = (flared && !thin) ? RT_SLAB_SLACK * fmaxf(1.0f, sqrtf(a))
+                                : fmaxf(RT_SLAB_SLACK, 1.02f * sqrtf(fmaf(7e-7f, fmaxf(1.0f, a), fmaxf(a - 1.0f, 0.0f))));
+    r.sqa = (flared && !thin) ? ((lens_free && a < 3e5f) ? sqrtf(a) : -sqrtf(fminf(a, 1e30f))) : 0.0f;
+    r.kappa = thin ? 0.998f * sqrtf(a) * (sqrtf(a) - sqrtf(a - 1.0f)) : 1.0f;
+    if (!(r.sqa == r.sqa)) { r.sqa = -1e15f; r.slack = RT_SLAB_SLACK; r.kappa = 1.0f; }
     return r;
 }
 template <bool ROBUST>
-__device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK) {
+__device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK,
+                                     float kappa = 1.0f) {
     float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
+    float rho = 0.0f;
     if (ROBUST) {
+        if (kappa != 1.0f) rho = 0.5005f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2) + 1e-6f;      // thin flare only
         const float dl = slack * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
         l0 -= dl; h0 += dl; l1 -= dl; h1 += dl; l2 -= dl; h2 += dl;
     }
@@ -265,7 +280,9 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     const float az = l2 * inv.z, bz = h2 * inv.z;
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
-    return t_near <= t_far && t_near <= t_best;
+    const bool pass = t_near <= t_far;
+    if (ROBUST && kappa != 1.0f) t_near = fmaxf(fmaf(kappa, t_near, -rho), 0.0f);                  // thin flare: bound of t, not the entry
+    return pass && t_near <= t_best;
 }
 // Box test of a FLARED ray (cold path; 8 % of the queries of C5, none of the default scene).  The accepted hits of such a ray
 // are not near the spheres they belong to (t0 = b - sqrt(dis) of an aligned sphere at distance L is ~0.6 L / |d| for a = 1.3)
@@ -303,7 +320,9 @@ __device__ __forceinline__ bool slab_flared_core(const float lo[3], const float 
             // arithmetic.  Boxes too large for a bound (c_min <= 0) are ordered by their distance: 1e-6 L <= 0.001 <= any t.
             const float L = sqrtf(Lmin2);
             float lb = 1e-6f * L;
-            if (c_min > 0.0f) lb = fmaxf(lb, fmaf(0.998f * sqa, L, -1.0001f * sqrtf(fmaf(a - 1.0f, Lmin2, rho2))));
+            // sqrt(a) L - sqrt((a - 1) L^2 + rho'^2) without the cancellation; rho'^2 = rho^2 + the rounding shell of dis
+            const float rho2s = fmaf(3e-6f * a, Lmin2, rho2);
+            if (Lmin2 > rho2s) lb = fmaxf(lb, 0.999f * (Lmin2 - rho2s) / fmaf(sqa, L, sqrtf(fmaf(a - 1.0f, Lmin2, rho2s))));
             if (lb <= t_best) { pass = true; t_near = fminf(t_near, lb); }
         }
     }
@@ -322,7 +341,7 @@ static __device__ __noinline__ bool slab_flared(float lx, float ly, float lz, fl
 // One child box of a node in the robust path: ordinary rays take the inflated slab, flared rays the cold routine above.
 __device__ __forceinline__ bool slab_robust(const float lo[3], const float hi[3], V3 o, V3 d, V3 inv, float t_best, float& t_near,
                                             const RaySlack rs, bool curved) {
-    if (rs.sqa == 0.0f) return slab<true>(lo, hi, o, inv, t_best, t_near, rs.slack);
+    if (rs.sqa == 0.0f) return slab<true>(lo, hi, o, inv, t_best, t_near, rs.slack, rs.kappa);
     if (rs.sqa < 0.0f) {                                                   // flared, lenses possible: full flare inflation, no distance pruning
         const float a = rs.sqa * rs.sqa;
         float tn;
@@ -833,7 +852,7 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
 
     Hit h;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f;
+    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f; rs.kappa = 1.0f;
     int stack[kBvhStack];
     int sp = 0, node = 0;
     bool traversing = false;
@@ -1108,6 +1127,34 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     }
 }
 
+// Warp-cooperative brute force over ALL leaves for the ray of lane `src` (called convergently by the 32 lanes).  For rays the
+// hierarchy cannot help: a very wide flare (|d|^2 > RT_BVH_BRUTE_A: the acceptance cone of the reference's sphere test opens
+// to nearly the forward half space, cos^2 = 1 / |d|^2), or any flared ray in a scene with lenses (no bound holds for them).
+// Such a ray walks most of the tree; done by one lane that is 10^5 dependent fetches (0.1 s for C5 — a handful of them, a few in
+// one pixel, made every launch last a second), done by the warp it is n_leaves / 32 coalesced rounds (60 us).  These rays are
+// rare (C5: |d|^2 > 16 for 2 in 10^4 queries).  Same leaf tests, winner by (t, id): exactly hitScene's result.
+#ifndef RT_BVH_BRUTE_A
+#define RT_BVH_BRUTE_A 16.0f
+#endif
+template <class A, bool COUNT>
+static __device__ __noinline__ void warp_brute_force(const float4* __restrict__ leaves, uint32_t n_leaves, int src, float ox, float oy, float oz,
+                                                     float dx, float dy, float dz, Hit* out, WorkCount* wc) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const V3 o = mk(__shfl_sync(RT_FULL, ox, src), __shfl_sync(RT_FULL, oy, src), __shfl_sync(RT_FULL, oz, src));
+    const V3 d = mk(__shfl_sync(RT_FULL, dx, src), __shfl_sync(RT_FULL, dy, src), __shfl_sync(RT_FULL, dz, src));
+    Hit b; b.t = RT_T_MAX; b.id = kIdMiss; b.bu = 0.0f; b.bv = 0.0f; b.aux = 0u;
+    WorkCount dummy; dummy.nodes = dummy.sph = dummy.len = dummy.tri = dummy.flared_nodes = dummy.flared_queries = 0u;
+    for (uint32_t i = lane; i < n_leaves; i += 32u) bvh_leaf<A, COUNT>(leaves + 4 * (size_t)i, o, d, b, COUNT ? wc : &dummy);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        Hit q;
+        q.t = __shfl_xor_sync(RT_FULL, b.t, off); q.id = __shfl_xor_sync(RT_FULL, b.id, off);
+        q.bu = __shfl_xor_sync(RT_FULL, b.bu, off); q.bv = __shfl_xor_sync(RT_FULL, b.bv, off); q.aux = __shfl_xor_sync(RT_FULL, b.aux, off);
+        if (closer(q.t, q.id, b)) b = q;
+    }
+    if ((int)lane == src && closer(b.t, b.id, *out)) *out = b;      // *out holds the plane hit (planes are not in the tree)
+}
+
 // LBVH flavour of trace_tail_body: lanes advance ONE node per trip of the traversal loop (see trace_body_bvh); a lane
 // whose traversal finished waits until `regen` lanes wait, then the waiting lanes close their path on a miss / light,
 // or shade the hit and start the bounced ray; finished paths restart from the stored head.
@@ -1123,6 +1170,15 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 #endif
 #ifndef RT_BVH_FLAG_SLAB
 #define RT_BVH_FLAG_SLAB 1
+#endif
+#ifndef RT_BVH_BRUTE_MAX_LEAVES
+#define RT_BVH_BRUTE_MAX_LEAVES 262144u   // a scan of more leaves than this costs the warp more than the walk costs the lane
+#endif
+#ifndef RT_BVH_BRUTE_SQA
+#define RT_BVH_BRUTE_SQA 4.0f       // sqrt(RT_BVH_BRUTE_A)
+#endif
+#ifndef RT_BVH_FLARE_COST
+#define RT_BVH_FLARE_COST 96       // flared lanes step when (their number) x (trips they waited) reaches this
 #endif
 template <class A, bool COUNT>
 __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
@@ -1140,7 +1196,15 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     const float4* S = p.sc.stream;
     const uint32_t lane = threadIdx.x & 31u;
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
-    const uint32_t k_end = p.first + p.n;
+    // Work items.  One lane renders all samples of a pixel in sample order — or, when the host asks for sample chunks
+    // (TraceLaunch::chunks > 1, fast arm + linear sums only), chunk_spp of them: a pixel behind a chain of glass spheres costs
+    // hundreds of times the average (its rays are flared and walk large parts of the tree), and with whole pixels as items a
+    // few such pixels, each serial in one lane, set the duration of the launch (C5, 32 spp: 1.1 s for 0.2 s of work).  Item
+    // q -> pixel q / chunks, chunk q % chunks: the lanes of a warp trace different samples of the same pixels.  Chunk sums go
+    // to partial[c][j]; k_combine_chunks adds them in chunk order (deterministic).
+    const uint32_t chunks = p.chunks > 1u ? p.chunks : 1u;
+    const uint32_t n_items = p.head.n_stoch * chunks;
+    uint32_t k_end = p.first + p.n;
     // Persistent lanes over a queue of stochastic pixels: path lengths in large scenes are heavy tailed (mirror and
     // glass chains up to the depth limit), so with one pixel per lane most lanes of a warp idled behind its slowest
     // pixel (ncu: 12.5 of 32 lanes traversing).  A lane renders all samples of its pixel in sample order (the
@@ -1148,7 +1212,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     PixelRng pr; pr.vec_base = pr.uni_base = pr.hp = 0u;
     float4* px = nullptr;
     float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    uint32_t k = k_end, i = 0u, mat_id = 0u;
+    uint32_t k = k_end, k_first = k_end, i = 0u, mat_id = 0u;
     V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f), out = mk(0.0f, 0.0f, 0.0f);
     Hit h; h.t = 0.0f; h.id = kIdMiss; h.bu = h.bv = 0.0f; h.aux = 0u;
     auto restart = [&]() {
@@ -1161,10 +1225,10 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
     WorkCount wc; wc.nodes = wc.sph = wc.len = wc.tri = wc.flared_nodes = wc.flared_queries = 0u;
     const uint32_t regen = p.bvh_regen ? p.bvh_regen : 8u;
     V3 inv = mk(0.0f, 0.0f, 0.0f);
-    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f;
+    RaySlack rs; rs.slack = RT_SLAB_SLACK; rs.sqa = 0.0f; rs.kappa = 1.0f;
     int sp = 0, node = 0;
-    bool traversing = false, has_ray = false, have_result = false, exhausted = false, flare_mode = false;
-    constexpr uint32_t kFlarePark = 12u;
+    bool traversing = false, has_ray = false, have_result = false, exhausted = false;
+    uint32_t flare_age = 0u;                                 // warp uniform: trips since the flared lanes last stepped
     auto push = [&](int v) {
         if (sp < RT_BVH_SSTACK) sst[sp * kTraceThreads] = v;
         else if (sp < kBvhStack) lst[sp - RT_BVH_SSTACK] = v;
@@ -1179,6 +1243,9 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
         if (traversing && node < 0) { bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~node), o, d, h, &wc); traversing = false; }
         inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
         rs = ray_slack(d, p.sc.n_len == 0u);
+        // a direction with an infinite or NaN component hits nothing finite: every sphere / lens root and every Moller-Trumbore
+        // parameter of such a ray is infinite or NaN and fails the range test (cl:127) — no need to walk the tree for it
+        if (!(fabsf(d.x) + fabsf(d.y) + fabsf(d.z) < 3.0e38f)) traversing = false;
         if (COUNT && rs.sqa != 0.0f) ++wc.flared_queries;
         have_result = true;
     };
@@ -1193,17 +1260,26 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
             if ((int)lane == leader) base = atomicAdd(p.queue, (uint32_t)__popc(nm));
             base = __shfl_sync(RT_FULL, base, leader);
             if (need) {
-                const uint32_t j = base + (uint32_t)__popc(nm & ((1u << lane) - 1u));
-                if (j < p.head.n_stoch) {
+                const uint32_t q = base + (uint32_t)__popc(nm & ((1u << lane) - 1u));
+                if (q < n_items) {
+                    const uint32_t j = chunks > 1u ? q / chunks : q, c = q - j * chunks;
                     const uint32_t slot = __ldg(p.head.list + j);
                     int x, y;
                     slot_pixel(slot, p.W, x, y);
 #pragma unroll
                     for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
                     pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
-                    px = p.target + (size_t)y * p.W + x;
-                    acc = (p.accum_mode == 1u || p.first > 0u) ? *px : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                    k = p.first; has_ray = true; have_result = false; traversing = false;
+                    if (chunks > 1u) {
+                        px = p.partial + ((size_t)c * p.head.n_stoch + j);
+                        acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                        k_first = min(p.first + c * p.chunk_spp, p.first + p.n);
+                        k_end = min(k_first + p.chunk_spp, p.first + p.n);
+                    } else {
+                        px = p.target + (size_t)y * p.W + x;
+                        acc = (p.accum_mode == 1u || p.first > 0u) ? *px : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                        k_first = p.first;
+                    }
+                    k = k_first; has_ray = k < k_end; have_result = false; traversing = false;
                     restart();
                 } else {
                     exhausted = true; px = nullptr;
@@ -1233,17 +1309,31 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 ++k; has_ray = k < k_end; restart();
             }
         }
-        for (;;) {                                           // ---- traversal: one node per trip
-            // Flared rays (rs.sqa != 0, slab_flared_core) need three times the instructions of an ordinary box test; mixed into
-            // ordinary trips every one of them would cost the warp a whole extra instruction stream (C5: 5 % of the queries,
-            // i.e. nearly every trip).  They are PARKED instead and traverse together in trips of their own (flare_mode, warp
-            // uniform): entered when kFlarePark lanes are parked or nothing else traverses, left when the last one is done.
-            {
-                const unsigned tf = __ballot_sync(RT_FULL, traversing && rs.sqa != 0.0f), tn = __ballot_sync(RT_FULL, traversing && rs.sqa == 0.0f);
-                if (!flare_mode) flare_mode = tf != 0u && (tn == 0u || (uint32_t)__popc(tf) >= kFlarePark);
-                else flare_mode = tf != 0u;
+        {                                                    // ---- rays the hierarchy cannot help: the warp scans the leaves
+            unsigned bm = __ballot_sync(RT_FULL, traversing && (rs.sqa < 0.0f || (rs.sqa > RT_BVH_BRUTE_SQA && p.bvh.n_leaves <= RT_BVH_BRUTE_MAX_LEAVES)));
+            while (bm) {
+                const int src = __ffs((int)bm) - 1;
+                bm &= bm - 1u;
+                warp_brute_force<A, COUNT>(p.bvh.leaves, p.bvh.n_leaves, src, o.x, o.y, o.z, d.x, d.y, d.z, &h, &wc);
+                if ((int)lane == src) traversing = false;
             }
-            if (traversing && (rs.sqa != 0.0f) == flare_mode) {
+        }
+        for (;;) {                                           // ---- traversal: one node per trip
+            // Wide-flared rays (rs.sqa != 0, slab_flared_core) need three to four times the instructions of an ordinary box test,
+            // and a warp pays them in full however few of its lanes are flared.  So flared lanes do not step every trip: they keep
+            // their place in the tree and wait until their step is worth its price — enough of them (count x trips waited >=
+            // RT_BVH_FLARE_COST, or 12 lanes), or nothing else left to advance.  Waiting is cheap (an idle lane of a warp that goes
+            // on), a step for one lane is not.
+            bool step;
+            {
+                const uint32_t tf = (uint32_t)__popc(__ballot_sync(RT_FULL, traversing && rs.sqa != 0.0f));
+                const bool any_n = __any_sync(RT_FULL, traversing && rs.sqa == 0.0f);
+                const bool do_f = tf != 0u && (!any_n || tf >= 12u || tf * flare_age >= (uint32_t)RT_BVH_FLARE_COST);
+                flare_age = (do_f || tf == 0u) ? 0u : flare_age + 1u;
+                step = traversing && (rs.sqa == 0.0f || do_f);
+            }
+            if (step) {
+                const bool flare_mode = rs.sqa != 0.0f;
                 const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
                 const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
@@ -1252,17 +1342,17 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 bool h0, h1;
                 if (COUNT) { ++wc.nodes; if (flare_mode) ++wc.flared_nodes; }
                 const uint32_t fl = __float_as_uint(n2.w);
-                if (flare_mode) {
+                if (RT_BVH_FLAG_SLAB && !A::kExact && fl == 0u) {           // triangles only: exact for every ray, flared or not
+                    h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
+                } else if (flare_mode) {
                     if (rs.sqa > 0.0f) {
                         h0 = slab_flared_core(lo0, hi0, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 1u) != 0u, p.sc.n_tri != 0u, t0);
                         h1 = slab_flared_core(lo1, hi1, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 2u) != 0u, p.sc.n_tri != 0u, t1);
                     } else {
                         h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
                     }
-                } else if (RT_BVH_FLAG_SLAB && !A::kExact && fl == 0u) {
-                    h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
                 } else {
-                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, rs.slack); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, rs.slack);
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, rs.slack, rs.kappa); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, rs.slack, rs.kappa);
                 }
                 int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
                 if (l0 == 0) { l0 = l1; l1 = 0; }
@@ -1377,7 +1467,8 @@ inline cudaError_t launch_tail_bvh(K kernel, TraceLaunch p, cudaStream_t s) {
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceThreads, 0)) != cudaSuccess) return e;
     const uint32_t T = kTraceThreads;
-    const uint32_t want = (p.head.n_stoch + T - 1u) / T, cap = (uint32_t)(sms * per_sm);
+    const uint64_t items = (uint64_t)p.head.n_stoch * (p.chunks > 1u ? p.chunks : 1u);
+    const uint32_t cap = (uint32_t)(sms * per_sm), want = (uint32_t)std::min<uint64_t>((items + T - 1u) / T, cap);
     p.tail_blocks = want < cap ? want : cap;
     const uint32_t rest_blocks = (p.head.n_slots - p.head.n_stoch + T - 1u) / T;
     if (p.tail_blocks + rest_blocks == 0u) return cudaSuccess;
