@@ -188,6 +188,18 @@ int rt_close_peers(rt_ctx* ctx);
 /* Probes used by the parity tests: nearest hit of arbitrary rays, and one bounce of the path loop.
  * rays6 = n x (origin.xyz, dir.xyz) on the host.  out_t/out_id may be NULL. */
 int rt_trace_rays(rt_ctx* ctx, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t);
+/* rt_trace_rays for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as rt_trace_rays in RT_ARITH_STRICT arithmetic (whatever rt_params.arith is),
+ * but the device scratch of the probe kernel — the rays, the ids and the parameters — is a static device array inside the
+ * library instead of per-call cudaMalloc: at most RT_NOALLOC_MAX_RAYS rays per call (RT_ERR_INVALID beyond that), 2 MiB held
+ * by every GPU that loads the library until the process exits.  The call performs no cudaMalloc / cudaFree and therefore
+ * builds nothing: if the scene's intersection structure (LBVH for large scenes) does not exist yet it fails with
+ * RT_ERR_STATE — call rt_trace_rays or any render call once beforehand.  All calls share the one array (it keeps the last
+ * call's contents; nothing needs to start at zero): calls that overlap on the GPU — several host threads, several contexts on
+ * one device — race on it. */
+#define RT_NOALLOC_MAX_RAYS 65536u
+int rt_trace_rays_noalloc(rt_ctx* ctx, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t);
 /* In-place bounce as work-item (gx, gy): rays6 updated, col3 = throughput after the bounce from (1,1,1),
  * ended[i] = 1 when the path terminated (miss or light). */
 int rt_bounce_rays(rt_ctx* ctx, float* rays6, uint32_t n, const uint32_t* sample, const uint32_t* bounce,

@@ -1194,6 +1194,34 @@ int rt_trace_rays(rt_ctx* c, const float* rays6, uint32_t n, uint32_t* out_id, f
     return RT_OK;
 }
 
+// No counterpart in the reference; added: rt_trace_rays for callers that may not
+// allocate (CUDA graph capture, serving loops).  Exact arithmetic whatever rt_params.arith says; at most RT_NOALLOC_MAX_RAYS
+// rays; calls no cudaMalloc / cudaFree — so it does not BUILD anything either: the intersection path of the scene (brute
+// force, or the LBVH) must be the one the parameters ask for already, which any render call or rt_trace_rays establishes.
+int rt_trace_rays_noalloc(rt_ctx* c, const float* rays6, uint32_t n, uint32_t* out_id, float* out_t) {
+    if (!c || !rays6) return fail(RT_ERR_INVALID, "rt_trace_rays_noalloc: null argument");
+    static_assert(RT_NOALLOC_MAX_RAYS == kNoAllocMaxRays, "header and kernel file agree on the size of the static scratch");
+    if (n > RT_NOALLOC_MAX_RAYS)
+        return fail(RT_ERR_INVALID, "rt_trace_rays_noalloc: %u rays exceed the static scratch of %u rays; split the batch or use rt_trace_rays", n, RT_NOALLOC_MAX_RAYS);
+    if (!c->have_scene) return fail(RT_ERR_STATE, "no scene uploaded");
+    if (n == 0) return RT_OK;
+    bool want_bvh = c->prm.accel == RT_ACCEL_BVH || (c->prm.accel == RT_ACCEL_AUTO && (c->staged_bytes > kMaxStagedBytes || c->n_finite > 512u));
+    if (c->n_finite == 0) want_bvh = false;
+    if (!want_bvh && c->staged_bytes > kMaxStagedBytes)
+        return fail(RT_ERR_UNSUPPORTED, "scene needs %zu bytes of shared memory for the brute-force path (max %zu)", c->staged_bytes, kMaxStagedBytes);
+    if (want_bvh && c->sc.n_tri > 0 && c->prm.mesh_mode != RT_MESH_NEAREST)
+        return fail(RT_ERR_UNSUPPORTED, "the LBVH path answers the nearest-front-facing mesh rule only: set mesh_mode = RT_MESH_NEAREST");
+    if (want_bvh != (c->bvh.n_leaves != 0))
+        return fail(RT_ERR_STATE, "rt_trace_rays_noalloc: the intersection structure of this scene is not in the state the parameters ask for (LBVH %s); "
+                                  "building or dropping it allocates — call rt_trace_rays or a render call once first", want_bvh ? "not built" : "still present");
+    Guard g(c);
+    if (!g.ok) return fail(RT_ERR_CUDA, "rt_trace_rays_noalloc: cannot make device %d current", c->device);
+    ProbeLaunch L = base_probe(c);
+    CU(launch_probe_hits_noalloc(L, rays6, n, out_id, out_t, c->stream));
+    c->stats.kernel_launches += 1;
+    return RT_OK;
+}
+
 int rt_bounce_rays(rt_ctx* c, float* rays6, uint32_t n, const uint32_t* sample, const uint32_t* bounce,
                    const uint32_t* gx, const uint32_t* gy, float* col3, uint8_t* ended) {
     if (!c || !rays6 || !sample || !bounce || !gx || !gy || !col3 || !ended) return fail(RT_ERR_INVALID, "rt_bounce_rays: null argument");

@@ -162,6 +162,9 @@ constexpr size_t kMaxBlockSmemBytes = 227 * 1024;   // opt-in limit of a block o
 cudaError_t launch_trace_strict(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_trace_fast(const TraceLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_hits_strict(const ProbeLaunch& p, cudaStream_t s);
+// rt_trace_rays_noalloc: Exact-arithmetic probe whose device scratch is a static device array (rt_kernels_strict.cu)
+constexpr uint32_t kNoAllocMaxRays = 65536u;
+cudaError_t launch_probe_hits_noalloc(ProbeLaunch p, const float* h_rays6, uint32_t n, uint32_t* h_id, float* h_t, cudaStream_t s);
 cudaError_t launch_probe_hits_fast(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_bounce_strict(const ProbeLaunch& p, cudaStream_t s);
 cudaError_t launch_probe_bounce_fast(const ProbeLaunch& p, cudaStream_t s);

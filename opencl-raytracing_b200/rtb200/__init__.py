@@ -22,6 +22,7 @@ ACCEL_AUTO, ACCEL_BRUTE, ACCEL_BVH = 0, 1, 2
 HEAD_ON, HEAD_OFF = 0, 1
 ID_MISS = 0xFFFFFFFF
 TABLE_FLOATS = 400000
+NOALLOC_MAX_RAYS = 65536
 
 
 class RtError(RuntimeError):
@@ -74,7 +75,7 @@ def lib():
         "rt_accum_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_image_device_ptr": [vp, C.POINTER(vp), C.POINTER(C.c_size_t)],
         "rt_set_accum_device_buffer": [vp, vp, C.c_size_t], "rt_set_finalize_target": [vp, vp, C.c_size_t],
-        "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
+        "rt_trace_rays": [vp, vp, u32, vp, vp], "rt_trace_rays_noalloc": [vp, vp, u32, vp, vp], "rt_bounce_rays": [vp, vp, u32, vp, vp, vp, vp, vp, vp],
         "rt_ipc_export": [vp, vp, vp], "rt_ipc_open_peers": [vp, ci, ci, vp, vp],
         "rt_set_peers_direct": [vp, ci, ci, C.POINTER(vp), vp], "rt_finalize_peers": [vp, u32], "rt_finalize_peers_async": [vp, u32], "rt_finalize_peers_barrier_async": [vp, u32], "rt_peer_barrier_status": [vp, C.POINTER(ci)], "rt_close_peers": [vp],
         "rt_measure_fp32_peak": [ci, C.POINTER(C.c_double), C.POINTER(C.c_double)],
@@ -351,6 +352,14 @@ class Context:
         ids = np.empty(r.shape[0], dtype=np.uint32)
         ts = np.empty(r.shape[0], dtype=np.float32)
         _check(self.L.rt_trace_rays(self.h, r.ctypes.data, r.shape[0], ids.ctypes.data, ts.ctypes.data))
+        return ids, ts
+
+    def trace_rays_noalloc(self, rays6):
+        """rt_trace_rays_noalloc: strict arithmetic, static device scratch, at most NOALLOC_MAX_RAYS rays."""
+        r = np.ascontiguousarray(rays6, dtype=np.float32).reshape(-1, 6)
+        ids = np.empty(r.shape[0], dtype=np.uint32)
+        ts = np.empty(r.shape[0], dtype=np.float32)
+        _check(self.L.rt_trace_rays_noalloc(self.h, r.ctypes.data, r.shape[0], ids.ctypes.data, ts.ctypes.data))
         return ids, ts
 
     def bounce_rays(self, rays6, sample, bounce, gx, gy):
