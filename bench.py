@@ -90,10 +90,14 @@ def parse():
                          "rt_finalize_peers_barrier_async: the ranks meet through arrival words in peer memory, no collective call); "
                          "fused_nccl_barriers = the same kernel between two NCCL all-reduces of a scalar (round 1); "
                          "nccl = one torch.distributed reduce to rank 0 + rt_finalize")
-    ap.add_argument("--split", default="pixels", choices=["pixels", "spp"],
+    ap.add_argument("--split", default="spp", choices=["pixels", "spp"],
                     help="N > 1: pixels = every rank renders all samples of its interleaved 128-pixel groups (rt_set_pixel_split; bit-identical "
                          "picture, work items as long as on one GPU); spp = every rank renders its share of the samples of the whole frame "
                          "(north_star's split, round 1)")
+    ap.add_argument("--host-image", default="rank0", choices=["shared", "rank0"],
+                    help="end-to-end read-back: rank0 = the exchange step writes rank 0's device image, rank 0 copies it to its pinned host "
+                         "buffer (rt_read_image); shared = every rank's finalize kernel stores its rows straight into ONE page-locked host image "
+                         "in shared memory over its own PCIe link (rt_set_finalize_target)")
     ap.add_argument("--no-heads", action="store_true", help="RT_HEAD_OFF: trace every segment of every sample (A/B of the path-head memoisation)")
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS),
                     help="BASELINE.json configs; the driver's default (and the headline) is c2")
@@ -387,26 +391,41 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     # ---- end to end through the C ABI with HOST buffers: every step uploads scene, textures, table (pinned host memory ->
     # device), renders, and the exchange / finalize step stores the picture straight into the caller's page-locked HOST image
     # (rt_set_finalize_target; N > 1: one shared host image, every rank writes its rows over its own PCIe link).
-    host_image = SharedHostImage(H, W, world, rank)
+    shared = a.host_image == "shared" or world == 1
+    host_image = SharedHostImage(H, W, world if shared else 1, rank)
     img_host = host_image.array
     tex_pinned = torch.from_numpy(tex).pin_memory()
     table_pinned = torch.from_numpy(table).pin_memory()
     h2d = tex_pinned.numel() * 4 + table_pinned.numel() * 4 + sum(v.nbytes for v in arr.values()) + 48
-    d2h = img_host.nbytes                        # the whole picture crosses PCIe once per step (1/N of it per rank)
+    d2h = img_host.nbytes                        # the whole picture crosses PCIe once per step
+
+    e2e_parts = {"upload": 0.0, "render_exchange": 0.0, "readback": 0.0}
 
     def e2e_step():
+        t_a = time.perf_counter()
         ctx.upload_textures(tex_pinned.numpy()); ctx.upload_scene(arr); ctx.set_random_table(table_pinned.numpy())
+        t_b = time.perf_counter()
         r, _ = step()
-        stream.synchronize()                     # rank 0: behind the last rank barrier, i.e. every rank's rows are in host memory
+        if shared:
+            stream.synchronize()                 # rank 0: behind the last rank barrier, i.e. every rank's rows are in host memory
+        t_c = time.perf_counter()
+        if not shared and rank == 0:
+            ctx.read_image(img_host)
+        t_d = time.perf_counter()
+        e2e_parts["upload"] += t_b - t_a; e2e_parts["render_exchange"] += t_c - t_b; e2e_parts["readback"] += t_d - t_c
         return r
 
-    ctx.set_finalize_target(host_image.ptr, host_image.nbytes)
+    if shared:
+        ctx.set_finalize_target(host_image.ptr, host_image.nbytes)
     e2e_step()
     sync_all()
     e2e_image_ok = bool(img_host[..., 3].min() == 1.0 and img_host[..., :3].max() > 0.1) if rank == 0 else True
+    for k_ in e2e_parts:
+        e2e_parts[k_] = 0.0
     t0 = time.perf_counter()
     e2e_rays = 0
-    e2e_steps = max(1, min(steps, 3))
+    # enough steps that the fixed cost of the closing device + rank synchronisation (a few ms) does not pose as per-step time
+    e2e_steps = max(steps, 10) if elapsed_ms / steps < 100.0 else max(1, min(steps, 3))
     for _ in range(e2e_steps):
         e2e_rays += e2e_step()
     sync_all()
@@ -506,8 +525,10 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "host_image_complete": e2e_image_ok,
+                    "rank0_ms_per_step": {k_: round(1e3 * v_ / e2e_steps, 3) for k_, v_ in e2e_parts.items()},
                     "what": "rt_upload_textures + rt_upload_scene + rt_set_random_table from pinned host memory, rt_render_samples, exchange + "
-                            "finalize storing the picture straight into the caller's page-locked host image (rt_set_finalize_target), every step"},
+                            "finalize " + ("storing the picture straight into the caller's page-locked host image (rt_set_finalize_target)" if shared
+                                         else "into rank 0's device image, rt_read_image into rank 0's pinned host buffer") + ", every step"},
             "gpu_launches": int(launches),
             "roofline": roofline,
         }
@@ -529,6 +550,23 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
     return out
 
 
+def pin_to_gpu_numa_node(gpu_index):
+    """One process per GPU: run this rank's host threads on the CPU cores next to its GPU (NVML's CPU affinity of the device), so
+    that the page-locked staging buffers it allocates are first touched on that NUMA node and its PCIe copies do not cross the
+    socket interconnect.  Best effort: without NVML, or where the mask is empty, nothing changes."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 PEAK = {"gslots": 0.0, "mhz": 0.0}
 PEAKS_FILE = {}
 
@@ -544,7 +582,12 @@ def main_b200(a, cfg):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    if world > 1:
+        pin_to_gpu_numa_node(local)
     torch.cuda.set_device(local)
+    # a real stream shared by the context (rt_set_stream), torch's fills and the NCCL collectives: torch's default stream is the
+    # null handle, which rt_set_stream reads as "the context's private stream"
+    torch.cuda.set_stream(torch.cuda.Stream())
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     PEAK["gslots"], PEAK["mhz"] = rtb200.measure_fp32_peak(local)

@@ -717,7 +717,8 @@ static int plan_chunks(rt_ctx* c, TraceLaunch& L) {
     }
     const uint64_t resident = (uint64_t)c->sm_count * 1024u, n_stoch = L.head.n_stoch;
     uint64_t chunks = (64u * resident + n_stoch - 1u) / n_stoch;
-    if (L.block_order) chunks = std::max<uint64_t>((L.n + 1023u) / 1024u, (4u * resident + n_stoch - 1u) / n_stoch);
+    // at least ~8 waves of blocks (a rank of the pixel split owns 1 / N of the pixels: N = 2 left 5.5 waves of whole pixels)
+    if (L.block_order) chunks = std::max<uint64_t>((L.n + 1023u) / 1024u, (8u * resident + n_stoch - 1u) / n_stoch);
     if (const char* e = std::getenv("RTB200_TAIL_CHUNKS")) chunks = (uint64_t)std::atoll(e);
     chunks = std::min<uint64_t>({chunks, L.n / 20u, (1ull << 31) / n_stoch});
     if (chunks < 2) return RT_OK;

@@ -23,6 +23,7 @@ def _main(out_path):
     from rtb200.multigpu import PeerFinalize, reduce_to_rank0, split_image_check
     world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
+    torch.cuda.set_stream(torch.cuda.Stream())       # a real stream: the null handle of torch's default stream would mean "private stream"
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     arr, tex8 = fx.default_scene()
     tex = fx.textures_to_float(tex8)
@@ -90,7 +91,7 @@ def test_two_rank_ipc_image_equals_single_rank_image(tmp_path):
     assert len(res) == 16
     for key, r in res.items():
         assert r["ok"], (key, r)
-        if key.endswith("/pixels"):
+        if key.endswith("/pixels") and key.startswith("strict/"):
             assert r["max_abs"] == 0.0, (key, r)
 
 
