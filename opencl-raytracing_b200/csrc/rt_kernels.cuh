@@ -265,13 +265,15 @@ __device__ __forceinline__ RaySlack ray_slack(V3 d, bool lens_free = true) {
     if (!(r.sqa == r.sqa)) { r.sqa = -1e15f; r.slack = RT_SLAB_SLACK; r.kappa = 1.0f; }
     return r;
 }
+// `thin`: some lane of the warp may carry a thin flare (kappa != 1) — a warp-uniform switch where the caller has one, so that
+// warps without such a ray do not issue the rho / kappa instructions at all.
 template <bool ROBUST>
 __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK,
-                                     float kappa = 1.0f) {
+                                     float kappa = 1.0f, bool thin = true) {
     float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
     float rho = 0.0f;
     if (ROBUST) {
-        if (kappa != 1.0f) rho = 0.5005f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2) + 1e-6f;      // thin flare only
+        if (thin) rho = kappa != 1.0f ? 0.5005f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2) + 1e-6f : 0.0f;   // thin flare only
         const float dl = slack * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
         l0 -= dl; h0 += dl; l1 -= dl; h1 += dl; l2 -= dl; h2 += dl;
     }
@@ -281,7 +283,7 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
     const bool pass = t_near <= t_far;
-    if (ROBUST && kappa != 1.0f) t_near = fmaxf(fmaf(kappa, t_near, -rho), 0.0f);                  // thin flare: bound of t, not the entry
+    if (ROBUST && thin) t_near = fmaxf(fmaf(kappa, t_near, -rho), 0.0f);   // thin flare: bound of t, not the entry (kappa = 1, rho = 0 else)
     return pass && t_near <= t_best;
 }
 // Box test of a FLARED ray (cold path; 8 % of the queries of C5, none of the default scene).  The accepted hits of such a ray
@@ -1318,14 +1320,17 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 if ((int)lane == src) traversing = false;
             }
         }
+        // warp-uniform switches of the traversal loop (rays only change in the block above): does any lane carry a wide flare
+        // (step rule, slab_flared_core), a thin one (rho / kappa arithmetic)?  Most warps of most scenes carry neither.
+        const bool warp_flared = __any_sync(RT_FULL, has_ray && rs.sqa != 0.0f), warp_thin = __any_sync(RT_FULL, has_ray && rs.kappa != 1.0f);
         for (;;) {                                           // ---- traversal: one node per trip
             // Wide-flared rays (rs.sqa != 0, slab_flared_core) need three to four times the instructions of an ordinary box test,
             // and a warp pays them in full however few of its lanes are flared.  So flared lanes do not step every trip: they keep
             // their place in the tree and wait until their step is worth its price — enough of them (count x trips waited >=
             // RT_BVH_FLARE_COST, or 12 lanes), or nothing else left to advance.  Waiting is cheap (an idle lane of a warp that goes
             // on), a step for one lane is not.
-            bool step;
-            {
+            bool step = traversing;
+            if (warp_flared) {
                 const uint32_t tf = (uint32_t)__popc(__ballot_sync(RT_FULL, traversing && rs.sqa != 0.0f));
                 const bool any_n = __any_sync(RT_FULL, traversing && rs.sqa == 0.0f);
                 const bool do_f = tf != 0u && (!any_n || tf >= 12u || tf * flare_age >= (uint32_t)RT_BVH_FLARE_COST);
@@ -1342,9 +1347,7 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 bool h0, h1;
                 if (COUNT) { ++wc.nodes; if (flare_mode) ++wc.flared_nodes; }
                 const uint32_t fl = __float_as_uint(n2.w);
-                if (RT_BVH_FLAG_SLAB && !A::kExact && fl == 0u) {           // triangles only: exact for every ray, flared or not
-                    h0 = slab<false>(lo0, hi0, o, inv, h.t, t0); h1 = slab<false>(lo1, hi1, o, inv, h.t, t1);
-                } else if (flare_mode) {
+                if (flare_mode && fl != 0u) {
                     if (rs.sqa > 0.0f) {
                         h0 = slab_flared_core(lo0, hi0, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 1u) != 0u, p.sc.n_tri != 0u, t0);
                         h1 = slab_flared_core(lo1, hi1, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 2u) != 0u, p.sc.n_tri != 0u, t1);
@@ -1352,7 +1355,13 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                         h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
                     }
                 } else {
-                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, rs.slack, rs.kappa); h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, rs.slack, rs.kappa);
+                    // ONE instruction stream for every lane: a child whose subtree holds triangles only (flag clear; fast arm) gets
+                    // slack 0 — the plain slab test, exact for Moller-Trumbore in any parametrisation — instead of a branch of its
+                    // own: with two branches the common half of the test was issued twice, at 13.5 lanes each (ncu, C4).
+                    const bool use_flags = RT_BVH_FLAG_SLAB && !A::kExact;
+                    const bool cv0 = !use_flags || (fl & 1u) != 0u, cv1 = !use_flags || (fl & 2u) != 0u;
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, cv0 ? rs.slack : 0.0f, cv0 ? rs.kappa : 1.0f, warp_thin);
+                    h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, cv1 ? rs.slack : 0.0f, cv1 ? rs.kappa : 1.0f, warp_thin);
                 }
                 int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
                 if (l0 == 0) { l0 = l1; l1 = 0; }
