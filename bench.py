@@ -542,6 +542,8 @@ def run_gpu_config(cfg, a, spp, steps, warmup, world, rank, local, with_clocks, 
             r = cpu_reference_rate(cfg, spp_step * (4 if cfg["name"] == "c2" else 1), reps, 1 if window is None else 0, window)
             out["cpu_baseline"] = {"value": round(r["rate"], 3), "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
     if peers is not None:
+        if a.reduce == "fused" and ctx.peer_barrier_timed_out():
+            raise SystemExit("bench.py: a device-side rank barrier gave up waiting (a rank never arrived): the numbers of this run are void")
         peers.close()
     ctx.close()
     host_image.close()

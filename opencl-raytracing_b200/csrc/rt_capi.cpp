@@ -1005,6 +1005,14 @@ int rt_set_finalize_target(rt_ctx* c, void* p, size_t bytes) {
     if (!p) { c->finalize_target = nullptr; return RT_OK; }
     if (bytes < (size_t)c->W * c->H * sizeof(float4)) return fail(RT_ERR_INVALID, "finalize target too small");
     if (((uintptr_t)p & 15u) != 0) return fail(RT_ERR_INVALID, "finalize target must be 16-byte aligned");
+    {   // page-locked host memory: the address the DEVICE uses for it is not the host address on every system
+        Guard g(c);
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return fail(RT_ERR_INVALID, "finalize target: not an address CUDA knows"); }
+        if (at.type == cudaMemoryTypeUnregistered || !at.devicePointer)
+            return fail(RT_ERR_INVALID, "finalize target is pageable host memory the device cannot reach (page-lock it: cudaHostRegister / cudaHostAlloc, mapped)");
+        p = at.devicePointer;
+    }
     c->finalize_target = (float4*)p;
     return RT_OK;
 }

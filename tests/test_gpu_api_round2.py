@@ -191,3 +191,29 @@ def test_pixel_split_parts_add_up_bit_for_bit(scenes, table):
             with pytest.raises(rt.RtError):
                 ctx.set_pixel_split(4, 4)
             ctx.set_pixel_split(1, 0)
+
+
+def test_finalize_target_in_mapped_host_memory(scenes, table):
+    """rt_set_finalize_target: rt_finalize stores the picture straight into page-locked host memory (no staging copy) and it equals
+    the image read back the ordinary way; pageable memory is refused."""
+    import torch
+    import rtb200 as rt
+    from rtb200 import fixtures as fx
+    W, H, spp = 320, 180, 8
+    cam = fx.camera(60, W / H)
+    host = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+    host.zero_()
+    with make_ctx(rt, scenes, "default", W, H, table, max_depth=10, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=4) as ctx:
+        ctx.clear_accum()
+        ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+        ctx.finalize(spp)
+        want = ctx.read_image().copy()
+        ctx.set_finalize_target(host.data_ptr(), host.numel() * 4)
+        ctx.finalize(spp)                                   # synchronous: the stores have landed
+        assert np.array_equal(bits(host.numpy()), bits(want))
+        pageable = np.zeros((H, W, 4), np.float32)
+        with pytest.raises(rt.RtError):
+            ctx.set_finalize_target(pageable.ctypes.data, pageable.nbytes)
+        with pytest.raises(rt.RtError):
+            ctx.set_finalize_target(host.data_ptr(), 16)
+        ctx.set_finalize_target(None, 0)
