@@ -94,7 +94,7 @@ def parse():
                     help="N > 1: pixels = every rank renders all samples of its interleaved 128-pixel groups (rt_set_pixel_split; bit-identical "
                          "picture, work items as long as on one GPU); spp = every rank renders its share of the samples of the whole frame "
                          "(north_star's split, round 1)")
-    ap.add_argument("--host-image", default="rank0", choices=["shared", "rank0"],
+    ap.add_argument("--host-image", default="shared", choices=["shared", "rank0"],
                     help="end-to-end read-back: rank0 = the exchange step writes rank 0's device image, rank 0 copies it to its pinned host "
                          "buffer (rt_read_image); shared = every rank's finalize kernel stores its rows straight into ONE page-locked host image "
                          "in shared memory over its own PCIe link (rt_set_finalize_target)")
