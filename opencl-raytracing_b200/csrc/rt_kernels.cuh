@@ -198,12 +198,32 @@ __device__ __forceinline__ bool closer(float t, uint32_t id, const Hit& best) {
 // One leaf = one primitive; its 64-byte record (DevBvh::leaves, leaf order = Morton order) holds the test data of the
 // primitive itself, so a leaf visit is one fetch of two sectors next to those of the neighbouring leaves, not an
 // index followed by a dependent fetch from the scene's stream.
+// One 64-byte record (a node or a leaf) in TWO 256-bit loads (LDG.E.256, sm_100) instead of four 128-bit ones: the LBVH render
+// kernel keeps the L1 load/store data pipe busier (68 % of its peak, ncu) than the issue slots (65 %), and three quarters of
+// its wavefronts are these fetches — one lane, one record, 32 different lines per instruction.
+#ifndef RT_LOAD256
+#define RT_LOAD256 1      // ptxas 12.9 crashes on ld.global.nc.v8.f32 in these kernels; v4.u64 compiles to the same LDG.E.ENL2.256
+#endif
+__device__ __forceinline__ void load64(const float4* __restrict__ p, float4& a, float4& b, float4& c, float4& d) {
+#if RT_LOAD256
+    unsigned long long u0, u1, u2, u3, v0, v1, v2, v3;
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(u0), "=l"(u1), "=l"(u2), "=l"(u3) : "l"(p));
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v0), "=l"(v1), "=l"(v2), "=l"(v3) : "l"(p + 2));
+    auto lo = [](unsigned long long x) { return __uint_as_float((unsigned)x); };
+    auto hi = [](unsigned long long x) { return __uint_as_float((unsigned)(x >> 32)); };
+    a = make_float4(lo(u0), hi(u0), lo(u1), hi(u1)); b = make_float4(lo(u2), hi(u2), lo(u3), hi(u3));
+    c = make_float4(lo(v0), hi(v0), lo(v1), hi(v1)); d = make_float4(lo(v2), hi(v2), lo(v3), hi(v3));
+#else
+    a = __ldg(p); b = __ldg(p + 1); c = __ldg(p + 2); d = __ldg(p + 3);
+#endif
+}
 // Work counters of the instrumented (untimed) LBVH render kernel: the numerator of the roofline of a BVH run is COUNTED
 // work, not the brute-force operation count.
 struct WorkCount { uint32_t nodes, sph, len, tri, flared_nodes, flared_queries; };
 template <class A, bool COUNT = false>
 __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 d, Hit& best, WorkCount* wc = nullptr) {
-    const float4 r0 = __ldg(L), r1 = __ldg(L + 1), r2 = __ldg(L + 2), r3 = __ldg(L + 3);
+    float4 r0, r1, r2, r3;
+    load64(L, r0, r1, r2, r3);
     const uint32_t id = __float_as_uint(r3.x), idx = __float_as_uint(r3.y), kind = id >> 28;
     if (kind == kKindSphere) {
         float t;
@@ -363,7 +383,8 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
     int sp = 0, node = bvh.root;
     for (;;) {
         const float4* N = reinterpret_cast<const float4*>(bvh.nodes + node);
-        const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+        float4 n0, n1, n2, n3;
+        load64(N, n0, n1, n2, n3);
         const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
@@ -873,7 +894,8 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
         for (;;) {                                           // ---- traversal: one node per trip
             if (traversing) {
                 const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
-                const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+                float4 n0, n1, n2, n3;
+                load64(N, n0, n1, n2, n3);
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
@@ -1340,7 +1362,8 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
             if (step) {
                 const bool flare_mode = rs.sqa != 0.0f;
                 const float4* N = reinterpret_cast<const float4*>(p.bvh.nodes + node);
-                const float4 n0 = __ldg(N), n1 = __ldg(N + 1), n2 = __ldg(N + 2), n3 = __ldg(N + 3);
+                float4 n0, n1, n2, n3;
+                load64(N, n0, n1, n2, n3);
                 const float lo0[3] = {n0.x, n0.y, n0.z}, hi0[3] = {n1.x, n1.y, n1.z}, lo1[3] = {n2.x, n2.y, n2.z}, hi1[3] = {n3.x, n3.y, n3.z};
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
