@@ -256,6 +256,9 @@ __device__ __forceinline__ void bvh_leaf(const float4* __restrict__ L, V3 o, V3 
 // Twelve more instructions per box; triangle-only nodes (BvhNode::flags == 0) do not need it in the fast arm — Moller-
 // Trumbore is exact in any parametrisation.
 #define RT_SLAB_SLACK 1.0e-3f
+#ifndef RT_SLAB_L2
+#define RT_SLAB_L2 1
+#endif
 // Per-ray constants of the box tests (a = |d|^2):
 //   ordinary ray (a - 1 <= 3e-6)       slack = 1e-3 (the round-1 value), kappa = 1, sqa = 0: inflated slab, pruned by its entry.
 //   THIN flare (3e-6 < a - 1 <= RT_BVH_THIN_FLARE, scene without lenses)   stays in the ordinary code path: the box is inflated
@@ -294,7 +297,16 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     float rho = 0.0f;
     if (ROBUST) {
         if (thin) rho = kappa != 1.0f ? 0.5005f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2) + 1e-6f : 0.0f;   // thin flare only
-        const float dl = slack * (fmaxf(fabsf(l0), fabsf(h0)) + fmaxf(fabsf(l1), fabsf(h1)) + fmaxf(fabsf(l2), fabsf(h2)));
+        // distance from the origin to the farthest corner of the box (>= |oc| of any centre inside): the Euclidean one — the
+        // sum of the three components, up to 1.73 times as much, tested 3 times as many leaf boxes of C5 as needed
+        const float m0 = fmaxf(fabsf(l0), fabsf(h0)), m1 = fmaxf(fabsf(l1), fabsf(h1)), m2 = fmaxf(fabsf(l2), fabsf(h2));
+#if RT_SLAB_L2
+        float far_corner;                                                  // approximate root (2 ulp): covered by the 1.00001
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(far_corner) : "f"(fmaf(m0, m0, fmaf(m1, m1, m2 * m2))));
+        const float dl = slack * 1.00001f * far_corner;
+#else
+        const float dl = slack * (m0 + m1 + m2);
+#endif
         l0 -= dl; h0 += dl; l1 -= dl; h1 += dl; l2 -= dl; h2 += dl;
     }
     const float ax = l0 * inv.x, bx = h0 * inv.x;
