@@ -7,6 +7,7 @@
 //   k_refit         one thread per leaf walks to the root; the second arrival at a node (atomic counter) merges
 //   k_emit_nodes    traversal layout: each node stores the boxes of its two children
 #include "rt_bvh.h"
+#include <cuda_fp16.h>
 
 #include <cfloat>
 #include <vector>
@@ -203,7 +204,9 @@ __global__ void k_emit_nodes(BvhBuildInput in, int n, const int2* children, cons
     for (int k = 0; k < 3; ++k) { nd.lo0[k] = a.lo[k]; nd.hi0[k] = a.hi[k]; nd.lo1[k] = b.lo[k]; nd.hi1[k] = b.hi[k]; }
     nd.child0 = ch.x; nd.child1 = ch.y;
     nd.flags = (uint32_t)child_curved<false>(ch.x, curved, leaf_info, sorted) | ((uint32_t)child_curved<false>(ch.y, curved, leaf_info, sorted) << 1);
-    nd.pad1 = 0u;
+    const float ra = 0.5005f * fminf(fminf(a.hi[0] - a.lo[0], a.hi[1] - a.lo[1]), a.hi[2] - a.lo[2]) + 1e-6f;
+    const float rb = 0.5005f * fminf(fminf(b.hi[0] - b.lo[0], b.hi[1] - b.lo[1]), b.hi[2] - b.lo[2]) + 1e-6f;
+    nd.rho = (uint32_t)__half_as_ushort(__float2half_ru(ra)) | ((uint32_t)__half_as_ushort(__float2half_ru(rb)) << 16);   // > 65504: inf, no bound
     nodes[i] = nd;
 }
 

@@ -13,7 +13,8 @@ struct alignas(16) BvhNode {
     float lo0[3]; int32_t child0;
     float hi0[3]; int32_t child1;
     float lo1[3]; uint32_t flags;     // bit 0 / 1: the subtree of child 0 / 1 holds a sphere or a lens (needs the inflated box test)
-    float hi1[3]; uint32_t pad1;
+    float hi1[3]; uint32_t rho;       // two binary16, child 0 low / child 1 high: an upper bound of the radius of any sphere inside the
+                                      // child's box (0.5005 x its smallest extent + 1e-6, rounded up) — the thin-flare bound of slab<true>
 };
 static_assert(sizeof(BvhNode) == 64, "one node = four 16-byte words");
 

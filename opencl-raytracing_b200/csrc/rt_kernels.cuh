@@ -20,6 +20,7 @@
 #include "rt_device.h"
 #include "rt_math.cuh"
 #include <algorithm>
+#include <cuda_fp16.h>
 
 namespace rtb {
 
@@ -290,13 +291,15 @@ __device__ __forceinline__ RaySlack ray_slack(V3 d, bool lens_free = true) {
 }
 // `thin`: some lane of the warp may carry a thin flare (kappa != 1) — a warp-uniform switch where the caller has one, so that
 // warps without such a ray do not issue the rho / kappa instructions at all.
+__device__ __forceinline__ float2 node_rho(float packed) {                // BvhNode::rho -> (child 0, child 1)
+    const uint32_t u = __float_as_uint(packed);
+    return make_float2(__half2float(__ushort_as_half((unsigned short)(u & 0xffffu))), __half2float(__ushort_as_half((unsigned short)(u >> 16))));
+}
 template <bool ROBUST>
 __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o, V3 inv, float t_best, float& t_near, float slack = RT_SLAB_SLACK,
-                                     float kappa = 1.0f, bool thin = true) {
+                                     float kappa = 1.0f, bool thin = true, float rho = 0.0f) {
     float l0 = lo[0] - o.x, h0 = hi[0] - o.x, l1 = lo[1] - o.y, h1 = hi[1] - o.y, l2 = lo[2] - o.z, h2 = hi[2] - o.z;
-    float rho = 0.0f;
     if (ROBUST) {
-        if (thin) rho = kappa != 1.0f ? 0.5005f * fminf(fminf(h0 - l0, h1 - l1), h2 - l2) + 1e-6f : 0.0f;   // thin flare only
         // distance from the origin to the farthest corner of the box (>= |oc| of any centre inside): the Euclidean one — the
         // sum of the three components, up to 1.73 times as much, tested 3 times as many leaf boxes of C5 as needed
         const float m0 = fmaxf(fabsf(l0), fabsf(h0)), m1 = fmaxf(fabsf(l1), fabsf(h1)), m2 = fmaxf(fabsf(l2), fabsf(h2));
@@ -315,7 +318,8 @@ __device__ __forceinline__ bool slab(const float lo[3], const float hi[3], V3 o,
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000004f;   // Ize 2013: robust exit
     const bool pass = t_near <= t_far;
-    if (ROBUST && thin) t_near = fmaxf(fmaf(kappa, t_near, -rho), 0.0f);   // thin flare: bound of t, not the entry (kappa = 1, rho = 0 else)
+    // thin flare: bound of t, not the entry; rho = BvhNode::rho of this child (>= the radius of any sphere inside the box)
+    if (ROBUST && thin) t_near = kappa != 1.0f ? fmaxf(fmaf(kappa, t_near, -rho), 0.0f) : t_near;
     return pass && t_near <= t_best;
 }
 // Box test of a FLARED ray (cold path; 8 % of the queries of C5, none of the default scene).  The accepted hits of such a ray
@@ -374,8 +378,8 @@ static __device__ __noinline__ bool slab_flared(float lx, float ly, float lz, fl
 }
 // One child box of a node in the robust path: ordinary rays take the inflated slab, flared rays the cold routine above.
 __device__ __forceinline__ bool slab_robust(const float lo[3], const float hi[3], V3 o, V3 d, V3 inv, float t_best, float& t_near,
-                                            const RaySlack rs, bool curved) {
-    if (rs.sqa == 0.0f) return slab<true>(lo, hi, o, inv, t_best, t_near, rs.slack, rs.kappa);
+                                            const RaySlack rs, bool curved, float rho) {
+    if (rs.sqa == 0.0f) return slab<true>(lo, hi, o, inv, t_best, t_near, rs.slack, rs.kappa, true, rho);
     if (rs.sqa < 0.0f) {                                                   // flared, lenses possible: full flare inflation, no distance pruning
         const float a = rs.sqa * rs.sqa;
         float tn;
@@ -401,7 +405,8 @@ __device__ __forceinline__ void hit_bvh(const DevScene& sc, const float4* __rest
         const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
         float t0, t1;
         const uint32_t fl = __float_as_uint(n2.w);
-        bool h0 = slab_robust(lo0, hi0, o, d, inv, best.t, t0, rs, (fl & 1u) != 0u), h1 = slab_robust(lo1, hi1, o, d, inv, best.t, t1, rs, (fl & 2u) != 0u);
+        const float2 rho = node_rho(n3.w);
+        bool h0 = slab_robust(lo0, hi0, o, d, inv, best.t, t0, rs, (fl & 1u) != 0u, rho.x), h1 = slab_robust(lo1, hi1, o, d, inv, best.t, t1, rs, (fl & 2u) != 0u, rho.y);
         if (h0 && c0 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c0), o, d, best); h0 = false; }
         if (h1 && c1 < 0) { bvh_leaf<A>(bvh.leaves + 4 * (~c1), o, d, best); h1 = false; }
         if (h0 && h1) {                                   // both internal: nearer first, the other on the stack
@@ -912,7 +917,8 @@ __device__ __forceinline__ void trace_body_bvh(const TraceLaunch& p) {
                 const int c0 = __float_as_int(n0.w), c1 = __float_as_int(n1.w);
                 float t0, t1;
                 const uint32_t fl = __float_as_uint(n2.w);
-                bool h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u), h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
+                const float2 rho = node_rho(n3.w);
+                bool h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u, rho.x), h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u, rho.y);
                 if (h0 && c0 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c0), o, d, h); h0 = false; }
                 if (h1 && c1 < 0) { bvh_leaf<A>(p.bvh.leaves + 4 * (~c1), o, d, h); h1 = false; }
                 if (h0 && h1) {
@@ -1382,12 +1388,13 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                 bool h0, h1;
                 if (COUNT) { ++wc.nodes; if (flare_mode) ++wc.flared_nodes; }
                 const uint32_t fl = __float_as_uint(n2.w);
+                const float2 rho = node_rho(n3.w);
                 if (flare_mode && fl != 0u) {
                     if (rs.sqa > 0.0f) {
                         h0 = slab_flared_core(lo0, hi0, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 1u) != 0u, p.sc.n_tri != 0u, t0);
                         h1 = slab_flared_core(lo1, hi1, o, d, inv, h.t, rs.slack, rs.sqa, (fl & 2u) != 0u, p.sc.n_tri != 0u, t1);
                     } else {
-                        h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u);
+                        h0 = slab_robust(lo0, hi0, o, d, inv, h.t, t0, rs, (fl & 1u) != 0u, rho.x); h1 = slab_robust(lo1, hi1, o, d, inv, h.t, t1, rs, (fl & 2u) != 0u, rho.y);
                     }
                 } else {
                     // ONE instruction stream for every lane: a child whose subtree holds triangles only (flag clear; fast arm) gets
@@ -1395,22 +1402,25 @@ __device__ __forceinline__ void trace_tail_bvh_body(const TraceLaunch& p) {
                     // own: with two branches the common half of the test was issued twice, at 13.5 lanes each (ncu, C4).
                     const bool use_flags = RT_BVH_FLAG_SLAB && !A::kExact;
                     const bool cv0 = !use_flags || (fl & 1u) != 0u, cv1 = !use_flags || (fl & 2u) != 0u;
-                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, cv0 ? rs.slack : 0.0f, cv0 ? rs.kappa : 1.0f, warp_thin);
-                    h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, cv1 ? rs.slack : 0.0f, cv1 ? rs.kappa : 1.0f, warp_thin);
+                    h0 = slab<true>(lo0, hi0, o, inv, h.t, t0, cv0 ? rs.slack : 0.0f, cv0 ? rs.kappa : 1.0f, warp_thin, rho.x);
+                    h1 = slab<true>(lo1, hi1, o, inv, h.t, t1, cv1 ? rs.slack : 0.0f, cv1 ? rs.kappa : 1.0f, warp_thin, rho.y);
                 }
-                int l0 = (h0 && c0 < 0) ? c0 : 0, l1 = (h1 && c1 < 0) ? c1 : 0;      // leaves are ~slot < 0; 0 = none
+                // children that passed, as one integer each: < 0 a leaf (~slot), > 0 an internal node, 0 none (node 0 is the root,
+                // never a child) — min / max instead of pairs of predicates
+                const int k0 = h0 ? c0 : 0, k1 = h1 ? c1 : 0;
+                int l0 = min(k0, 0), l1 = min(k1, 0);
                 if (l0 == 0) { l0 = l1; l1 = 0; }
                 while (l0 != 0) {
                     bvh_leaf<A, COUNT>(p.bvh.leaves + 4 * (~l0), o, d, h, &wc);
                     l0 = l1; l1 = 0;
                 }
-                h0 = h0 && c0 >= 0; h1 = h1 && c1 >= 0;
-                if (h0 && h1) {
+                // the sibling of a leaf that was just hit may now lie behind the hit (t_near is a lower bound of its hits)
+                const int i0 = t0 <= h.t ? max(k0, 0) : 0, i1 = t1 <= h.t ? max(k1, 0) : 0;
+                if (i0 != 0 && i1 != 0) {
                     const bool first0 = t0 <= t1;
-                    push(first0 ? c1 : c0);
-                    node = first0 ? c0 : c1;
-                } else if (h0) node = c0;
-                else if (h1) node = c1;
+                    push(first0 ? i1 : i0);
+                    node = first0 ? i0 : i1;
+                } else if ((i0 | i1) != 0) node = i0 | i1;
                 else if (sp > 0) node = pop();
                 else traversing = false;
             }
