@@ -795,6 +795,7 @@ static int do_render(rt_ctx* c, const float* cam, uint32_t first, uint32_t n, ui
     L.rng_mode = c->prm.rng_mode; L.seed = c->prm.seed; L.accum_mode = accum_mode; L.mesh_mode = c->prm.mesh_mode;
     L.target = accum_mode == RT_ACCUM_SUM ? c->d_accum : c->d_image;
     L.rays = c->d_rays;
+    { const char* e = std::getenv("RTB200_TAIL_STEAL"); L.steal = (e && std::atoi(e) == 0) ? 0u : 1u; }   // sample stealing, TraceLaunch::steal
     L.queries = c->d_rays + 1;
     L.queue = reinterpret_cast<uint32_t*>(c->d_rays + 3);
     const bool use_head = c->prm.path_head == RT_HEAD_ON;

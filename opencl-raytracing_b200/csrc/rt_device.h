@@ -100,6 +100,11 @@ struct TraceLaunch {
     // the chunks of a pixel in chunk order.  chunks <= 1: one item per pixel, summed straight into `target`.
     uint32_t chunks, chunk_spp;
     float4* partial;
+    // Sample stealing (k_trace_tail_fast, linear sums): a lane out of samples takes half of the unstarted samples of the busiest
+    // lane of its warp.  Reproducible for the same call; the ORDER in which a pixel's samples are added then depends on the other
+    // pixels of the warp, so sums of different partitions of a frame (regions, pixel split, block order) agree to rounding, not bit
+    // for bit.  RTB200_TAIL_STEAL=0 turns it off.
+    uint32_t steal;
     // Longest blocks first (k_trace_tail_*, brute-force path).  A "pixel block" is kTraceThreads consecutive entries of
     // the stochastic list; block_cost[pb] (written when non-null) = queries the block executed; block_order (when
     // non-null) = pixel blocks by decreasing cost: block i of the grid renders chunk i % chunks of pixel block

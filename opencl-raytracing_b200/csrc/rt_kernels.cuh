@@ -1084,6 +1084,9 @@ __device__ __forceinline__ void terminal_body(const TraceLaunch& p, uint32_t j) 
     *px = acc;
 }
 
+#ifndef RT_STEAL
+#define RT_STEAL 1                  // brute-force render kernel, fast arm: idle lanes take samples from busy ones
+#endif
 // trace + retrace + getCol for samples [first, first+n) of the stochastic pixels, restarting from the path heads.
 // Every lane entering a trip holds a pending hit on a surface that is neither a miss nor a light: the trip shades it,
 // traces the bounced ray, and closes the path on a miss (cl:450-452), a light (cl:459-462) or at the depth limit.  So
@@ -1119,7 +1122,7 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
 #pragma unroll
     for (uint32_t r = 0; r < 4u; ++r) hs[r * kTraceThreads] = __ldg(p.head.rec + r * p.head.n_slots + slot);
 
-    const PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
+    PixelRng pr = make_pixel_rng((uint32_t)x, (uint32_t)y, (uint32_t)p.W, p.seed);
     ShadeEnv env; env.sc = &p.sc; env.tex = &p.tex; env.table = p.table; env.rng_mode = p.rng_mode;
     float4* px = chunks > 1u ? p.partial + ((size_t)c * p.head.n_stoch + j) : p.target + (size_t)y * p.W + x;
     float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -1130,16 +1133,60 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     uint32_t i, mat_id;
     V3 o, d, out;
     Hit h;
+    const float4* hsp = hs;                                  // restart state of the pixel this lane works on
     auto restart = [&]() {
-        const float4 r0 = hs[0], r1 = hs[kTraceThreads], r2 = hs[2 * kTraceThreads], r3 = hs[3 * kTraceThreads];
+        const float4 r0 = hsp[0], r1 = hsp[kTraceThreads], r2 = hsp[2 * kTraceThreads], r3 = hsp[3 * kTraceThreads];
         o = mk(r0.x, r0.y, r0.z); d = mk(r1.x, r1.y, r1.z); out = mk(r2.x, r2.y, r2.z);
         h.t = r0.w; h.bu = r1.w; h.bv = r2.w;
         i = __float_as_uint(r3.x); h.id = __float_as_uint(r3.y); h.aux = __float_as_uint(r3.z); mat_id = __float_as_uint(r3.w);
     };
     restart();
     uint32_t queries = 0u;
+    // Sample stealing (fast arm, linear sums).  A warp lives as long as its slowest lane, and the lanes' totals differ: the
+    // pixels differ, and so do sums of n random path lengths (by ~2 / sqrt(n) of the mean between the extremes of 32 lanes) —
+    // 2 of 32 lanes idle over a launch of 1024 samples per lane (ncu), more for shorter items (one rank of an 8-way sample
+    // split).  A lane that has run out of samples takes the upper half of the samples not yet started of the lane that has
+    // most left, with that pixel's RNG key and restart state, sums them in an accumulator of its own (`sacc`) and hands the sum
+    // to the owner of the pixel (`owner`, a lane of this warp) when it steals again or the warp ends.  One steal per trip; which
+    // lane steals what depends on the paths alone, so the picture stays reproducible bit for bit, but a pixel's samples are
+    // added in another order than sample order — the strict arm and the reference's sqrt(mean) chain never steal.
+    const bool steal = RT_STEAL && !A::kExact && p.accum_mode == 1u && p.steal != 0u;
+    float4 sacc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    uint32_t owner = lane, root = lane;                      // owner of the stolen samples in `sacc`; pixel of the samples in work
+    auto hand_over = [&](unsigned from) {                    // the warp: every lane in `from` gives its sacc to its owner
+        for (; from; from &= from - 1u) {
+            const int src = __ffs((int)from) - 1;
+            const float4 v = make_float4(__shfl_sync(RT_FULL, sacc.x, src), __shfl_sync(RT_FULL, sacc.y, src),
+                                         __shfl_sync(RT_FULL, sacc.z, src), __shfl_sync(RT_FULL, sacc.w, src));
+            const uint32_t to = __shfl_sync(RT_FULL, owner, src);
+            if (lane == to) { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+            if ((int)lane == src) { sacc = make_float4(0.0f, 0.0f, 0.0f, 0.0f); owner = lane; }
+        }
+    };
 
-    while (__any_sync(RT_FULL, k < k_end)) {
+    for (;;) {
+        const unsigned busy = __ballot_sync(RT_FULL, k < k_end);
+        if (busy == 0u) break;
+        if (steal && busy != RT_FULL) {                      // warp uniform
+            // victim: most samples not yet started (the one in work stays where it is)
+            const uint32_t spare = k < k_end ? k_end - k - 1u : 0u;
+            const uint32_t top = __reduce_max_sync(RT_FULL, (min(spare, 0x03ffffffu) << 5) | lane);
+            if ((top >> 5) != 0u) {
+                const int v = (int)(top & 31u), t = __ffs((int)~busy) - 1;
+                hand_over(__ballot_sync(RT_FULL, (int)lane == t && owner != lane));      // the thief's previous loot first
+                const uint32_t take = ((top >> 5) + 1u) >> 1;
+                const uint32_t v_end = __shfl_sync(RT_FULL, k_end, v), v_root = __shfl_sync(RT_FULL, root, v);
+                const uint32_t vb = __shfl_sync(RT_FULL, pr.vec_base, v), ub = __shfl_sync(RT_FULL, pr.uni_base, v), hp = __shfl_sync(RT_FULL, pr.hp, v);
+                if ((int)lane == v) k_end -= take;
+                if ((int)lane == t) {
+                    k = v_end - take; k_end = v_end;
+                    pr.vec_base = vb; pr.uni_base = ub; pr.hp = hp;
+                    root = v_root; owner = v_root;
+                    hsp = hs - lane + v_root;
+                    restart();
+                }
+            }
+        }
         const bool active = k < k_end;
         if (active) { shade<A>(env, S, h, mat_id, pr, o, d, out, k, i); ++i; }
         const bool q = active && i < p.depth;
@@ -1158,9 +1205,14 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
                     }
                 }
             }
-            if (ended) { accumulate_sample<A>(acc, out, k, p.accum_mode); ++k; restart(); }
+            if (ended) {
+                if (root == lane) accumulate_sample<A>(acc, out, k, p.accum_mode);
+                else accumulate_sample<A>(sacc, out, k, p.accum_mode);
+                ++k; restart();
+            }
         }
     }
+    if (steal) hand_over(__ballot_sync(RT_FULL, owner != lane));
     if (live) *px = acc;
     queries = __reduce_add_sync(RT_FULL, queries);                                   // < 2^32 per warp launch
     if (lane == 0u && queries) {

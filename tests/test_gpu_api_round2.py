@@ -59,15 +59,48 @@ def test_deferred_render_again_equals_eager_schedule(scenes, table, monkeypatch,
     assert a[4] < b[4]                              # fewer launches for the same picture
 
 
-def test_region_renders_the_same_pixels_as_the_full_frame(scenes, table):
+def same_sums(a, b, exact):
+    """Accumulation buffers of the same samples: bit for bit, or (fast arm with sample stealing, TraceLaunch::steal: the samples
+    of a pixel are added in an order that depends on the other pixels of its warp) equal to rounding, sample counts exact."""
+    if exact:
+        return np.array_equal(bits(a), bits(b))
+    return np.array_equal(a[..., 3], b[..., 3]) and np.allclose(a[..., :3], b[..., :3], rtol=1e-5, atol=1e-5)
+
+
+def test_sample_stealing_is_reproducible_and_keeps_the_sums(scenes, table, monkeypatch):
+    """TraceLaunch::steal (k_trace_tail_fast, linear sums): lanes out of samples take samples of the busiest lane of their warp.
+    The same call gives the same bits every time; against the launch without stealing the samples are the same ones (sample
+    counts, rays and queries equal) added in another order (sums equal to rounding)."""
+    import rtb200 as rt
+    from rtb200 import fixtures as fx
+    W, H, spp = 320, 200, 48
+    cam = fx.camera(60, W / H)
+    res = {}
+    for key, env in (("on_a", "1"), ("on_b", "1"), ("off", "0")):
+        monkeypatch.setenv("RTB200_TAIL_STEAL", env)
+        with make_ctx(rt, scenes, "default", W, H, table, max_depth=12, arith=rt.ARITH_FAST, rng_mode=rt.RNG_COUNTER_TABLE, seed=9) as ctx:
+            ctx.clear_accum()
+            ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
+            st = ctx.stats()
+            res[key] = (ctx.read_accum().copy(), st.rays_last, st.queries_last)
+    assert np.array_equal(bits(res["on_a"][0]), bits(res["on_b"][0]))
+    assert res["on_a"][1:] == res["on_b"][1:] == res["off"][1:]
+    assert same_sums(res["on_a"][0], res["off"][0], exact=False)
+    assert not np.array_equal(bits(res["on_a"][0]), bits(res["off"][0]))       # stealing did happen
+    assert np.all(res["on_a"][0][..., 3] == spp)
+
+
+def test_region_renders_the_same_pixels_as_the_full_frame(scenes, table, monkeypatch):
     """rt_set_region: the work-items of a window are those of the full frame (same primary rays, same RNG keys), everything
-    outside keeps its contents; bad windows are refused."""
+    outside keeps its contents; bad windows are refused.  Strict arm, and fast arm without sample stealing: bit for bit."""
     import rtb200 as rt
     from rtb200 import fixtures as fx
     W, H, spp = 400, 240, 6
     cam = fx.camera(60, W / H)
     x0, y0, w, h = 123, 57, 90, 101
-    for arith in (rt.ARITH_STRICT, rt.ARITH_FAST):
+    for arith, stealing in ((rt.ARITH_STRICT, True), (rt.ARITH_FAST, True), (rt.ARITH_FAST, False)):
+        monkeypatch.setenv("RTB200_TAIL_STEAL", "1" if stealing else "0")
+        exact = arith == rt.ARITH_STRICT or not stealing
         for head in (rt.HEAD_ON, rt.HEAD_OFF):
             with make_ctx(rt, scenes, "default", W, H, table, max_depth=10, arith=arith, rng_mode=rt.RNG_COUNTER_TABLE, seed=3, path_head=head) as ctx:
                 ctx.clear_accum()
@@ -79,7 +112,7 @@ def test_region_renders_the_same_pixels_as_the_full_frame(scenes, table):
                 ctx.render_samples(cam, 0, spp, rt.ACCUM_SUM)
                 part = ctx.read_accum().copy()
                 rays_part = ctx.stats().rays_last
-                assert np.array_equal(bits(part[y0:y0 + h, x0:x0 + w]), bits(full[y0:y0 + h, x0:x0 + w]))
+                assert same_sums(part[y0:y0 + h, x0:x0 + w], full[y0:y0 + h, x0:x0 + w], exact)
                 part[y0:y0 + h, x0:x0 + w] = 0
                 assert not part.any() and 0 < rays_part < rays_full
                 ctx.set_region()                                   # back to the whole frame
@@ -162,16 +195,21 @@ def test_failed_lbvh_build_is_an_error_not_a_half_built_tree(table, monkeypatch)
         assert ctx.stats().bvh_nodes == 1500 and np.isfinite(ctx.read_image()).all()
 
 
-def test_pixel_split_parts_add_up_bit_for_bit(scenes, table):
+def test_pixel_split_parts_add_up_bit_for_bit(scenes, table, monkeypatch):
     """rt_set_pixel_split: the parts of a frame (interleaved 128-pixel groups, all samples each) rendered one after the
     other are disjoint, cover the frame, and their sum IS the single-context accumulation buffer — in both arms, with path
-    heads on and off, brute force and LBVH."""
+    heads on and off, brute force and LBVH (fast arm, brute force: bit for bit without sample stealing, to rounding with it)."""
     import rtb200 as rt
     from rtb200 import fixtures as fx
     W, H, spp = 400, 236, 10
     cam = fx.camera(60, W / H)
-    for arith, head, accel, mesh in ((rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT), (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT),
-                                     (rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_BVH, rt.MESH_NEAREST), (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_BVH, rt.MESH_NEAREST)):
+    for arith, head, accel, mesh, stealing in ((rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT, False),
+                                               (rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT, True),
+                                               (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_AUTO, rt.MESH_FIRST_FRONT, True),
+                                               (rt.ARITH_FAST, rt.HEAD_ON, rt.ACCEL_BVH, rt.MESH_NEAREST, True),
+                                               (rt.ARITH_STRICT, rt.HEAD_OFF, rt.ACCEL_BVH, rt.MESH_NEAREST, True)):
+        monkeypatch.setenv("RTB200_TAIL_STEAL", "1" if stealing else "0")
+        exact = not (stealing and arith == rt.ARITH_FAST and accel == rt.ACCEL_AUTO)     # the LBVH kernel has no stealing
         with make_ctx(rt, scenes, "default", W, H, table, max_depth=12, arith=arith, rng_mode=rt.RNG_COUNTER_TABLE, seed=6, path_head=head,
                       accel=accel, mesh_mode=mesh) as ctx:
             ctx.clear_accum()
@@ -187,7 +225,7 @@ def test_pixel_split_parts_add_up_bit_for_bit(scenes, table):
                     assert not (parts[..., 3] * a[..., 3]).any()            # disjoint
                     parts += a
                     rays += ctx.stats().rays_last
-            assert np.array_equal(bits(parts), bits(whole)) and rays == rays_whole
+            assert same_sums(parts, whole, exact) and rays == rays_whole
             with pytest.raises(rt.RtError):
                 ctx.set_pixel_split(4, 4)
             ctx.set_pixel_split(1, 0)

@@ -267,17 +267,21 @@ def test_sample_chunks_change_only_the_summation_order(rt, scenes, table, monkey
     assert not np.array_equal(res[7][0], base[0])            # the chunked path really ran
 
 
-@pytest.mark.parametrize("arith,accum", [("strict", "reference"), ("strict", "sum"), ("fast", "sum")])
+@pytest.mark.parametrize("arith,accum", [("strict", "reference"), ("strict", "sum"), ("fast", "sum"), ("fast", "sum-stealing")])
 def test_longest_blocks_first_changes_nothing(rt, scenes, table, monkeypatch, arith, accum):
     """Frames of >= 2048 pixel blocks: the first two samples of a call are a pilot launch that counts the queries of every
     block of 128 stochastic pixels, the rest is launched with the most expensive blocks first (and the order is kept
     while the path heads are valid).  Only the dispatch order changes: images, segment and query counts are bit-identical
-    to the launch in list order (fast arm: with whole pixels as work items in both)."""
+    to the launch in list order (fast arm: with whole pixels as work items in both, and without sample stealing — with it the
+    pilot launch changes which lane adds which sample, and the sums agree to rounding)."""
     from rtb200 import fixtures as fx
     W, H, spp = 1024, 576, 40
     cam = fx.camera(60, W / H)
     A = rt.ARITH_STRICT if arith == "strict" else rt.ARITH_FAST
     mode = rt.ACCUM_REFERENCE if accum == "reference" else rt.ACCUM_SUM
+    stealing = accum == "sum-stealing"
+    accum = "sum" if stealing else accum
+    monkeypatch.setenv("RTB200_TAIL_STEAL", "1" if stealing else "0")
     monkeypatch.setenv("RTB200_TAIL_CHUNKS", "1")
     res = {}
     for lpt in ("0", "1"):
@@ -295,7 +299,11 @@ def test_longest_blocks_first_changes_nothing(rt, scenes, table, monkeypatch, ar
             res[lpt] = (first, second, l1 - l0, st.kernel_launches - l1)
     off, on = res["0"], res["1"]
     for a, b in ((off[0], on[0]), (off[1], on[1])):
-        assert np.array_equal(bits(a[0]), bits(b[0])) and a[1] == b[1] and a[2] == b[2]
+        if stealing:
+            assert np.array_equal(a[0][..., 3], b[0][..., 3]) and np.allclose(a[0][..., :3], b[0][..., :3], rtol=1e-5, atol=1e-5)
+        else:
+            assert np.array_equal(bits(a[0]), bits(b[0]))
+        assert a[1] == b[1] and a[2] == b[2]
     assert on[2] == off[2] + 3 and on[3] == off[3]           # pilot + sort (2 launches) once, then the cached order
     if accum == "sum":
         assert np.all(on[1][0][..., 3] == 2 * spp)

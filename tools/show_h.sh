@@ -1,7 +1,7 @@
 #!/bin/bash
 # print the bench lines of a gpu_run_h.sh call.  usage: show_h.sh TAG variant
 cd /root/repo/gpurun_out
-for c in c2 c3 c1; do for f in r02h_$1_$c r02h_$1_$2_$c; do python - $f.json <<'PY'
+for c in c2 c3 c1 c2s; do for f in r02h_$1_$c r02h_$1_$2_$c; do python - $f.json <<'PY'
 import json,sys
 try:
     d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
