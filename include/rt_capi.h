@@ -110,7 +110,10 @@ int rt_set_region(rt_ctx* ctx, int x0, int y0, int w, int h);
  * unit a block of the render kernels owns) numbered in launch order; this context renders group g iff g % n_parts == part
  * and leaves all other pixels untouched.  Every pixel keeps its full-frame primary ray, RNG keys and ALL its samples in
  * sample order, so the parts of a frame rendered by different contexts add up to the single-context picture BIT FOR BIT
- * (each pixel has exactly one non-zero contribution).  n_parts <= 1 restores the whole frame. */
+ * (each pixel has exactly one non-zero contribution) in strict arithmetic; in fast arithmetic the lanes of a warp of the
+ * brute-force render kernel share their samples (TraceLaunch::steal), the samples of a pixel are the same but
+ * added in an order that depends on its warp, and the pictures agree to rounding (bit for bit again with RTB200_TAIL_STEAL=0).
+ * n_parts <= 1 restores the whole frame. */
 int rt_set_pixel_split(rt_ctx* ctx, int n_parts, int part);
 
 /* RayTracer::render (src/raytracer.cpp:127-144): sample_counter = 0, one sample, overwrites the image. */

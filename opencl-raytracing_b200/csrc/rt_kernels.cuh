@@ -1133,8 +1133,9 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     uint32_t i, mat_id;
     V3 o, d, out;
     Hit h;
-    const float4* hsp = hs;                                  // restart state of the pixel this lane works on
+    uint32_t root = lane;                                    // the lane whose pixel this lane works on (sample stealing below)
     auto restart = [&]() {
+        const float4* hsp = hs - lane + root;                // restart state of that pixel
         const float4 r0 = hsp[0], r1 = hsp[kTraceThreads], r2 = hsp[2 * kTraceThreads], r3 = hsp[3 * kTraceThreads];
         o = mk(r0.x, r0.y, r0.z); d = mk(r1.x, r1.y, r1.z); out = mk(r2.x, r2.y, r2.z);
         h.t = r0.w; h.bu = r1.w; h.bv = r2.w;
@@ -1147,20 +1148,19 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
     // 2 of 32 lanes idle over a launch of 1024 samples per lane (ncu), more for shorter items (one rank of an 8-way sample
     // split).  A lane that has run out of samples takes the upper half of the samples not yet started of the lane that has
     // most left, with that pixel's RNG key and restart state, sums them in an accumulator of its own (`sacc`) and hands the sum
-    // to the owner of the pixel (`owner`, a lane of this warp) when it steals again or the warp ends.  One steal per trip; which
+    // to the owner of the pixel (`root`, a lane of this warp) when it steals again or the warp ends.  One steal per trip; which
     // lane steals what depends on the paths alone, so the picture stays reproducible bit for bit, but a pixel's samples are
     // added in another order than sample order — the strict arm and the reference's sqrt(mean) chain never steal.
     const bool steal = RT_STEAL && !A::kExact && p.accum_mode == 1u && p.steal != 0u;
     float4 sacc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    uint32_t owner = lane, root = lane;                      // owner of the stolen samples in `sacc`; pixel of the samples in work
-    auto hand_over = [&](unsigned from) {                    // the warp: every lane in `from` gives its sacc to its owner
+    auto hand_over = [&](unsigned from) {                    // the warp: every lane in `from` gives its sacc to the owner of the pixel
         for (; from; from &= from - 1u) {
             const int src = __ffs((int)from) - 1;
             const float4 v = make_float4(__shfl_sync(RT_FULL, sacc.x, src), __shfl_sync(RT_FULL, sacc.y, src),
                                          __shfl_sync(RT_FULL, sacc.z, src), __shfl_sync(RT_FULL, sacc.w, src));
-            const uint32_t to = __shfl_sync(RT_FULL, owner, src);
+            const uint32_t to = __shfl_sync(RT_FULL, root, src);
             if (lane == to) { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
-            if ((int)lane == src) { sacc = make_float4(0.0f, 0.0f, 0.0f, 0.0f); owner = lane; }
+            if ((int)lane == src) sacc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         }
     };
 
@@ -1173,7 +1173,7 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
             const uint32_t top = __reduce_max_sync(RT_FULL, (min(spare, 0x03ffffffu) << 5) | lane);
             if ((top >> 5) != 0u) {
                 const int v = (int)(top & 31u), t = __ffs((int)~busy) - 1;
-                hand_over(__ballot_sync(RT_FULL, (int)lane == t && owner != lane));      // the thief's previous loot first
+                hand_over(__ballot_sync(RT_FULL, (int)lane == t && root != lane));       // the thief's previous loot first
                 const uint32_t take = ((top >> 5) + 1u) >> 1;
                 const uint32_t v_end = __shfl_sync(RT_FULL, k_end, v), v_root = __shfl_sync(RT_FULL, root, v);
                 const uint32_t vb = __shfl_sync(RT_FULL, pr.vec_base, v), ub = __shfl_sync(RT_FULL, pr.uni_base, v), hp = __shfl_sync(RT_FULL, pr.hp, v);
@@ -1181,8 +1181,7 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
                 if ((int)lane == t) {
                     k = v_end - take; k_end = v_end;
                     pr.vec_base = vb; pr.uni_base = ub; pr.hp = hp;
-                    root = v_root; owner = v_root;
-                    hsp = hs - lane + v_root;
+                    root = v_root;
                     restart();
                 }
             }
@@ -1212,7 +1211,7 @@ __device__ __forceinline__ void trace_tail_body(const TraceLaunch& p, float4* sm
             }
         }
     }
-    if (steal) hand_over(__ballot_sync(RT_FULL, owner != lane));
+    if (steal) hand_over(__ballot_sync(RT_FULL, root != lane));
     if (live) *px = acc;
     queries = __reduce_add_sync(RT_FULL, queries);                                   // < 2^32 per warp launch
     if (lane == 0u && queries) {
