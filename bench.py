@@ -91,8 +91,8 @@ def parse():
                          "fused_nccl_barriers = the same kernel between two NCCL all-reduces of a scalar (round 1); "
                          "nccl = one torch.distributed reduce to rank 0 + rt_finalize")
     ap.add_argument("--split", default="spp", choices=["pixels", "spp"],
-                    help="N > 1: pixels = every rank renders all samples of its interleaved 128-pixel groups (rt_set_pixel_split; bit-identical "
-                         "picture, work items as long as on one GPU); spp = every rank renders its share of the samples of the whole frame "
+                    help="N > 1: pixels = every rank renders all samples of its interleaved 128-pixel groups (rt_set_pixel_split; picture bit-identical "
+                         "in the strict arm, equal to rounding in the fast arm; work items as long as on one GPU); spp = every rank renders its share of the samples of the whole frame "
                          "(north_star's split, round 1)")
     ap.add_argument("--host-image", default="shared", choices=["shared", "rank0"],
                     help="end-to-end read-back: rank0 = the exchange step writes rank 0's device image, rank 0 copies it to its pinned host "
